@@ -1,0 +1,324 @@
+/*
+ * ottomarcher.h — C ABI of the B200 (sm_100a) renderer that replaces the CPU render threads of
+ * octaviogarcia/RaytracingOneWeekend ("ottomarcher").
+ *
+ * The seam it replaces is the free function
+ *     render_thread::render(&cam,&wrld,max_depth,tmin,tmax,samples_per_pixel,image_width,
+ *                           image_height,pixels_box,tid,&assigned_thread,&samples_atom)
+ * (reference src/render_thread.rs:145-147, called once per CPU thread from src/main.rs:207-213).
+ * One om_render handle stands for ALL of those threads: `tid`/`assigned_thread` become the
+ * device/partition fields of om_render_params.
+ *
+ * Every struct is a plain-old-data mirror of the Rust struct named beside it (f32/u32/u64 only,
+ * natural alignment, no padding surprises) so that a `#[repr(C)]` conversion on the Rust side is
+ * mechanical (see INTEGRATION.md and rust/ottomarcher-cuda-sys).  Matrices are row-major, i.e.
+ * m[4*row+col] == Mat4x4.e[row].e[col] (reference src/math/mat4x4.rs:7-10).
+ *
+ * Nothing in this header needs CUDA, C++ or torch types.
+ */
+#ifndef OTTOMARCHER_H
+#define OTTOMARCHER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define OM_API __declspec(dllexport)
+#else
+#define OM_API __attribute__((visibility("default")))
+#endif
+
+/* ------------------------------------------------------------------------------------------ */
+/* status codes (the reference panics; nothing here aborts or throws across the boundary)      */
+typedef enum om_status {
+    OM_OK = 0,
+    OM_ERR_INVALID = 1,     /* bad argument / bad handle state                                 */
+    OM_ERR_CUDA = 2,        /* a CUDA runtime call failed; om_last_error() has the text         */
+    OM_ERR_UNSUPPORTED = 3, /* e.g. Arc<dyn Traced>/Arc<dyn Marched> user types (hits.rs:39-40)  */
+    OM_ERR_OOM = 4,
+    OM_ERR_NO_DEVICE = 5    /* no CUDA device: there is NO CPU fallback in this library          */
+} om_status;
+
+/* ------------------------------------------------------------------------------------------ */
+/* materials.rs:11-23  (enum MaterialType + struct Material, 24 bytes)                          */
+enum { OM_MAT_LAMBERTIAN = 0, OM_MAT_METAL = 1, OM_MAT_DIELECTRIC = 2 };
+typedef struct om_material {
+    float albedo[3]; /* Lambertian, Metal */
+    float fuzz;      /* Metal             */
+    float ior;       /* Dielectric        */
+    uint32_t mat_type;
+} om_material;
+
+/* traced.rs:13-19 Sphere: unit sphere under an affine map (ellipsoids allowed).               */
+typedef struct om_sphere {
+    float m_local_to_world[16];
+    float m_world_to_local[16]; /* Mat4x4::fast_homogenous_inverse of the above (mat4x4.rs:59) */
+    om_material material;
+} om_sphere;
+
+/* traced.rs:229-235 Cube: cube of half-size 0.5 under an affine map.                          */
+typedef struct om_cube {
+    float m_local_to_world[16];
+    float m_world_to_local[16];
+    om_material material;
+} om_cube;
+
+/* traced.rs:77-82 InfinitePlane                                                              */
+typedef struct om_infinite_plane {
+    float center[3];
+    float normal[3]; /* unit */
+    om_material material;
+} om_infinite_plane;
+
+/* traced.rs:118-131 Barycentric<BT>; Parallelogram = BT 0, Triangle = BT 1 (traced.rs:225-226) */
+typedef struct om_barycentric {
+    float origin[3];
+    float u[3];
+    float u_length;
+    float v[3];
+    float v_length;
+    float uxv[3];
+    float uxvxu[3];
+    float base_inv[9]; /* Mat3x3 row-major */
+    float v_in_base[3];
+    om_material material;
+} om_barycentric;
+
+/* marched.rs:49-54 */
+typedef struct om_marched_sphere {
+    float center[3];
+    float radius;
+    om_material material;
+} om_marched_sphere;
+
+/* marched.rs:78-83 */
+typedef struct om_marched_box {
+    float center[3];
+    float sizes[3];
+    om_material material;
+} om_marched_box;
+
+/* marched.rs:104-113 */
+typedef struct om_marched_torus {
+    float m_local_to_world_translate_rotate[16];
+    float m_world_to_local_translate_rotate[16];
+    float m_local_to_world_scale[4];
+    float m_world_to_local_scale[4];
+    float sizes[3]; /* (R, r, unused) */
+    om_material material;
+} om_marched_torus;
+
+/* camera.rs:9-29 Camera (all fields, same order)                                             */
+typedef struct om_camera {
+    float origin[3];
+    float horizontal[3];
+    float vertical[3];
+    float lower_left_corner[3];
+    float u_of_plane[3];
+    float v_of_plane[3];
+    float w_of_plane[3];
+    float lens_radius;
+    float aspect_ratio;
+    float focus_dist;
+    float viewport_width;
+    float viewport_height;
+} om_camera;
+
+/* render_thread.rs:9-17 Stats, as read by the viewer (main.rs:228-232,249,287,377).
+ * `c` of Pixel (render_thread.rs:44) is never written by the reference and is not mirrored.  */
+typedef struct om_pixel {
+    float sum[3];
+    uint32_t n;
+    float avg_depth;
+    uint32_t bad_avgs;
+    uint64_t bloom; /* BloomFilter.state, utils.rs:76-78 */
+    uint8_t color[3];
+    uint8_t _pad[5];
+} om_pixel; /* 40 bytes */
+
+/* Object identity.  The reference uses the object's address (utils.rs:110); across the ABI an
+ * object is (type tag << 32) | (index in its list + 1); 0 stays "sky" (render_thread.rs:122). */
+enum {
+    OM_TYPE_SPHERE = 1, OM_TYPE_CUBE = 2, OM_TYPE_TRIANGLE = 3, OM_TYPE_INFINITE_PLANE = 4,
+    OM_TYPE_PARALLELOGRAM = 5, OM_TYPE_MARCHED_SPHERE = 6, OM_TYPE_MARCHED_BOX = 7,
+    OM_TYPE_MARCHED_TORUS = 8
+};
+#define OM_OBJ_ID(type, index) ((((uint64_t)(type)) << 32) | ((uint64_t)(index) + 1u))
+
+/* ------------------------------------------------------------------------------------------ */
+/* render flags                                                                                */
+enum {
+    /* retire a pixel when its 8-bit colour was unchanged for 5 samples in a row — the ONLY
+     * behaviour of the reference (render_thread.rs:31-38,194-198).  Off = fixed spp.          */
+    OM_RENDER_ADAPTIVE = 1u << 0,
+    /* kernels compiled with FMA contraction off and IEEE div/sqrt: bit-identical to the CPU
+     * oracle sample by sample.  Off = the fast build of the same kernels.                     */
+    OM_RENDER_EXACT = 1u << 1,
+    /* closest hit by linear scan in the reference's list order (hits.rs:270-286), no BVH.     */
+    OM_RENDER_BRUTE_FORCE = 1u << 2,
+    /* wavefront pipeline (raygen / intersect / shade / compact kernels) instead of the
+     * persistent path-regeneration kernel.                                                    */
+    OM_RENDER_WAVEFRONT = 1u << 3,
+    /* keep primitives and BVH in global memory even if they fit in shared memory.             */
+    OM_RENDER_NO_SMEM_SCENE = 1u << 4
+};
+
+typedef struct om_render_params {
+    uint32_t width;       /* image_width   (render_thread.rs:146)                              */
+    uint32_t height;      /* image_height                                                      */
+    uint32_t spp_max;     /* samples_per_pixel: a MAXIMUM in adaptive mode                      */
+    uint32_t max_depth;   /* max_depth     (main.rs:146)                                       */
+    float tmin;           /* main.rs:205                                                       */
+    float tmax;           /* main.rs:206                                                       */
+    uint64_t seed;        /* Philox key; replaces the OS-seeded thread_rng (utils.rs:25)        */
+    uint32_t flags;       /* OM_RENDER_*                                                       */
+    /* spp-slice partition: this handle renders samples [sample_base, sample_base+sample_count)
+     * of every pixel it owns.  sample_count 0 means spp_max - sample_base.                    */
+    uint32_t sample_base;
+    uint32_t sample_count;
+    /* interleaved-chunk partition, the analogue of `tid`/`assigned_thread` (main.rs:172-189):
+     * pixel p belongs to this handle iff (p / OM_CHUNK_PIXELS) % part_world == part_rank.      */
+    uint32_t part_rank;
+    uint32_t part_world;  /* 0 or 1 = own every pixel                                          */
+    int32_t device;       /* CUDA device ordinal, -1 = current device                          */
+} om_render_params;
+
+#define OM_CHUNK_PIXELS 2730u /* 32 KiB / sizeof(Color), main.rs:174-175 */
+
+typedef struct om_scene om_scene;   /* HittableList, then FrozenHittableList after freeze       */
+typedef struct om_render om_render; /* the N render threads + their shared Vec<Pixel>           */
+
+/* ------------------------------------------------------------------------------------------ */
+/* scene: HittableList (hits.rs:37-43) — one list per concrete type, `world += &obj` ≙ add_*   */
+OM_API om_status om_scene_create(om_scene** out);                 /* HittableList::new hits.rs:72 */
+OM_API om_status om_scene_clear(om_scene* s);                     /* HittableList::clear hits.rs:81 */
+OM_API om_status om_scene_destroy(om_scene* s);                   /* NULL is fine                */
+OM_API om_status om_scene_add_spheres(om_scene* s, const om_sphere* a, size_t n);          /* hits.rs:101-105 */
+OM_API om_status om_scene_add_cubes(om_scene* s, const om_cube* a, size_t n);
+OM_API om_status om_scene_add_triangles(om_scene* s, const om_barycentric* a, size_t n);
+OM_API om_status om_scene_add_infinite_planes(om_scene* s, const om_infinite_plane* a, size_t n);
+OM_API om_status om_scene_add_parallelograms(om_scene* s, const om_barycentric* a, size_t n);
+OM_API om_status om_scene_add_marched_spheres(om_scene* s, const om_marched_sphere* a, size_t n);
+OM_API om_status om_scene_add_marched_boxes(om_scene* s, const om_marched_box* a, size_t n);
+OM_API om_status om_scene_add_marched_tori(om_scene* s, const om_marched_torus* a, size_t n);
+/* `world += Arc<dyn Traced>` / `Arc<dyn Marched>` (hits.rs:91-100): user trait objects cannot
+ * cross to a device.  Always returns OM_ERR_UNSUPPORTED; present so the binding is total.     */
+OM_API om_status om_scene_add_dyn_object(om_scene* s, const void* trait_object);
+/* counts per list, order: spheres,cubes,triangles,infinite_planes,parallelograms,
+ * marched_spheres,marched_boxes,marched_tori */
+OM_API om_status om_scene_counts(const om_scene* s, uint64_t counts[8]);
+/* HittableList::freeze (hits.rs:87-89).  Builds the BVH that subsumes CameraHash
+ * (camera_hash.rs, hits.rs:116-185) from the objects' world bounding boxes
+ * (bounding_box.rs:69-73).  `cam` may be NULL (the BVH does not depend on the camera).         */
+OM_API om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags);
+/* statistics of the frozen scene: [0] bvh nodes, [1] bvh depth, [2] primitives in the BVH,
+ * [3] primitives kept in the always-test list, [4] bytes of the device scene image,
+ * [5] 1 if that image fits in shared memory */
+OM_API om_status om_scene_stats(const om_scene* s, uint64_t stats[6]);
+
+/* ------------------------------------------------------------------------------------------ */
+/* render: render_thread::render (render_thread.rs:145-202)                                    */
+OM_API om_status om_render_create(om_render** out, const om_scene* frozen, const om_camera* cam,
+                                  const om_render_params* params);
+OM_API om_status om_render_destroy(om_render* r); /* NULL is fine */
+/* Trace up to `spp_this_pass` more samples of every live pixel (sample-major passes, the
+ * reference's outer loop render_thread.rs:176).  Asynchronous.  0 = all remaining samples.    */
+OM_API om_status om_render_launch(om_render* r, uint32_t spp_this_pass);
+OM_API om_status om_render_sync(om_render* r);
+/* the AtomicU64 progress counter (main.rs:148, render_thread.rs:196-198): +1 per sample, plus
+ * all left-over samples of a pixel at the moment it retires.  Synchronises.                   */
+OM_API om_status om_render_samples_done(om_render* r, uint64_t* credited);
+/* samples actually traced (what Msamples/s counts).  Synchronises.                            */
+OM_API om_status om_render_samples_traced(om_render* r, uint64_t* traced);
+/* device time of the launches since the last call to this function, in ms (CUDA events on the
+ * render stream).  Synchronises.                                                              */
+OM_API om_status om_render_elapsed_ms(om_render* r, float* ms, uint32_t* launches);
+/* Vec<Pixel> read-out (what draw_to_sdl reads racily, main.rs:371).  `n` must be width*height. */
+OM_API om_status om_render_read_pixels(om_render* r, om_pixel* host, size_t n);
+/* MODE_NORMAL view (main.rs:374-381): tightly packed RGB24, width*height*3 bytes.             */
+OM_API om_status om_render_read_rgb(om_render* r, uint8_t* host_rgb, size_t nbytes);
+/* reset every pixel to Pixel::new() (render_thread.rs:47-50) and the counters to 0.           */
+OM_API om_status om_render_reset(om_render* r);
+
+/* Parity hook: primary-ray closest hit for every pixel — (obj_id, t), t = +INF and id 0 on a
+ * miss — i.e. what ray_color returns as (depthf, obj_id) (render_thread.rs:132-135).
+ * mode 0: pixel-centre ray (i_rand = j_rand = 0.5) without lens offset;
+ * mode 1: the ray sample `sample_index` of the pixel would use (Philox jitter + thin lens).   */
+OM_API om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_index,
+                                   uint64_t* ids, float* t, size_t n);
+
+/* Multi-GPU plumbing.  Export the accumulators into / import from caller-owned DEVICE memory
+ * (e.g. a torch tensor) so that any collective library can combine them.
+ *   acc   : width*height*8 floats  {sum.r,sum.g,sum.b,n, n*avg_depth, bad_avgs, 0, 0}
+ *   bloom : width*height uint64
+ * om_render_import_accum replaces the handle's pixels by the combined values and re-derives
+ * colour (utils.rs:12-17).                                                                   */
+OM_API om_status om_render_export_accum(om_render* r, float* dev_acc, uint64_t* dev_bloom);
+OM_API om_status om_render_import_accum(om_render* r, const float* dev_acc, const uint64_t* dev_bloom);
+/* dst[i] |= src[k][i] for k < nsrc: the bitwise-OR NCCL does not have. Device pointers.       */
+OM_API om_status om_bloom_or(uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc, size_t n,
+                             int32_t device);
+
+/* Parity hook: closest hit of arbitrary rays against a frozen scene, on the device, with the
+ * semantics of FrozenHittableList::hit (hits.rs:270-334).  dirs are normalised first like
+ * Ray::new (ray.rs:11-13).  Host arrays: origins/dirs n*3 floats in; ids n, t n, points n*3,
+ * normals n*3 out (any out pointer may be NULL).  flags: OM_RENDER_EXACT / _BRUTE_FORCE /
+ * _NO_SMEM_SCENE.                                                                             */
+OM_API om_status om_trace_rays(const om_scene* frozen, const float* origins, const float* dirs,
+                               size_t n, float tmin, float tmax, uint32_t flags, int32_t device,
+                               uint64_t* ids, float* t, float* points, float* normals);
+
+/* ------------------------------------------------------------------------------------------ */
+/* Host-side constructors: the reference keeps these in Rust; they are exported for hosts that
+ * are not the Rust crate (the C++ mirror in ottomarcher.hpp, the Python tests and bench).     */
+OM_API void om_camera_new(om_camera* out, const float lookfrom[3], const float lookat[3],
+                          const float vup[3], float vfov_in_degrees, float aspect_ratio,
+                          float aperture, float focus_dist);              /* camera.rs:38-59   */
+OM_API void om_material_lambertian(om_material* out, const float albedo[3]);   /* materials.rs:26 */
+OM_API void om_material_metal(om_material* out, const float albedo[3], float fuzz); /* :29-34  */
+OM_API void om_material_dielectric(om_material* out, float ior);               /* materials.rs:35 */
+OM_API void om_sphere_new(om_sphere* out, const float m_local_to_world[16], const om_material* m); /* traced.rs:22 */
+OM_API void om_sphere_new_with_radius(om_sphere* out, const float o[3], float r, const om_material* m); /* traced.rs:26 */
+OM_API void om_cube_new(om_cube* out, const float m_local_to_world[16], const om_material* m);   /* traced.rs:238 */
+OM_API void om_cube_new_with_length(om_cube* out, const float o[3], float len, const om_material* m); /* traced.rs:242 */
+OM_API void om_infinite_plane_new(om_infinite_plane* out, const float center[3], const float normal[3],
+                                  const om_material* m);                       /* traced.rs:86  */
+OM_API void om_barycentric_new3points(om_barycentric* out, const float origin[3], const float upoint[3],
+                                      const float vpoint[3], const om_material* m); /* traced.rs:148 */
+OM_API void om_marched_torus_new(om_marched_torus* out, const float m_local_to_world[16],
+                                 const float local_sizes[3], const om_material* m); /* marched.rs:115 */
+/* m4x4!(..) helpers (mat4x4.rs:88-123,167-209).  out = a ^ b is om_mat4_mul.                  */
+OM_API void om_mat4_identity(float out[16]);
+OM_API void om_mat4_translate(float out[16], float x, float y, float z);
+OM_API void om_mat4_scale(float out[16], float x, float y, float z);
+OM_API void om_mat4_rotate_x(float out[16], float f);
+OM_API void om_mat4_rotate_y(float out[16], float f);
+OM_API void om_mat4_rotate_z(float out[16], float f);
+OM_API void om_mat4_mul(float out[16], const float a[16], const float b[16]);
+OM_API void om_mat4_fast_homogenous_inverse(float out[16], const float m[16]);
+
+/* Seeded scene generators (synthetic inputs for tests and benchmarks).  They
+ * append to `s`.  Kinds:
+ *   0 random_scene of main.rs:37-100 (Philox in place of thread_rng)
+ *   1 basic_scene  of main.rs:102-110
+ *   2 rtiow_classic: random_scene without torus / parallelogram / triangle / cube
+ *   3 marched scene (marched ground sphere + 8x8 grid of marched sphere/box/torus)
+ *   4 random_scene with >= 60 % dielectric small spheres (glass-heavy)
+ *   5 n_param spheres in a 200 x 4 x 200 slab over the ground sphere (BVH stress)             */
+OM_API om_status om_scene_generate(om_scene* s, uint32_t kind, uint64_t seed, uint64_t n_param);
+
+/* ------------------------------------------------------------------------------------------ */
+OM_API const char* om_last_error(void); /* thread-local, never NULL */
+OM_API const char* om_version(void);
+OM_API int32_t om_device_count(void);
+/* FP32 FMA microbenchmark on `device`: achieved TFLOP/s (2 flop per FMA lane) and SM clock.    */
+OM_API om_status om_bench_fp32_peak(int32_t device, float* tflops, float* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OTTOMARCHER_H */
