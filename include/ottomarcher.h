@@ -164,7 +164,10 @@ enum {
      * persistent path-regeneration kernel.                                                    */
     OM_RENDER_WAVEFRONT = 1u << 3,
     /* keep primitives and BVH in global memory even if they fit in shared memory.             */
-    OM_RENDER_NO_SMEM_SCENE = 1u << 4
+    OM_RENDER_NO_SMEM_SCENE = 1u << 4,
+    /* instrumented kernels: count segments, BVH node visits, primitive tests, SDF evaluations
+     * (the executed-work figures of the FP32 roofline accounting); slower.                    */
+    OM_RENDER_COUNTERS = 1u << 5
 };
 
 typedef struct om_render_params {
@@ -211,6 +214,9 @@ OM_API om_status om_scene_add_dyn_object(om_scene* s, const void* trait_object);
 /* counts per list, order: spheres,cubes,triangles,infinite_planes,parallelograms,
  * marched_spheres,marched_boxes,marched_tori */
 OM_API om_status om_scene_counts(const om_scene* s, uint64_t counts[8]);
+/* copy list `which` (0 spheres .. 7 marched_tori, the order of om_scene_counts) back to the caller;
+ * nbytes must be count * sizeof(element).  Lets a host hand a generated scene to another consumer. */
+OM_API om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out, size_t nbytes);
 /* HittableList::freeze (hits.rs:87-89).  Builds the BVH that subsumes CameraHash
  * (camera_hash.rs, hits.rs:116-185) from the objects' world bounding boxes
  * (bounding_box.rs:69-73).  `cam` may be NULL (the BVH does not depend on the camera).         */
@@ -225,6 +231,9 @@ OM_API om_status om_scene_stats(const om_scene* s, uint64_t stats[6]);
 OM_API om_status om_render_create(om_render** out, const om_scene* frozen, const om_camera* cam,
                                   const om_render_params* params);
 OM_API om_status om_render_destroy(om_render* r); /* NULL is fine */
+/* Run this handle's work on a caller-owned CUDA stream (a cudaStream_t, e.g. torch's current
+ * stream) instead of the handle's own; NULL switches back.  The caller keeps ownership.        */
+OM_API om_status om_render_set_stream(om_render* r, void* cuda_stream);
 /* Trace up to `spp_this_pass` more samples of every live pixel (sample-major passes, the
  * reference's outer loop render_thread.rs:176).  Asynchronous.  0 = all remaining samples.    */
 OM_API om_status om_render_launch(om_render* r, uint32_t spp_this_pass);
@@ -234,6 +243,10 @@ OM_API om_status om_render_sync(om_render* r);
 OM_API om_status om_render_samples_done(om_render* r, uint64_t* credited);
 /* samples actually traced (what Msamples/s counts).  Synchronises.                            */
 OM_API om_status om_render_samples_traced(om_render* r, uint64_t* traced);
+/* all 16 device counters: [0] credited [1] traced [2] (internal) [3] segments [4] BVH node visits
+ * [5] primitive tests [6] SDF evaluations [7] march steps [8] normal evaluations
+ * [9] segments that entered the march loop.  [3..9] need OM_RENDER_COUNTERS.  Synchronises.  */
+OM_API om_status om_render_perf_counters(om_render* r, uint64_t out[16]);
 /* device time of the launches since the last call to this function, in ms (CUDA events on the
  * render stream).  Synchronises.                                                              */
 OM_API om_status om_render_elapsed_ms(om_render* r, float* ms, uint32_t* launches);
@@ -300,6 +313,11 @@ OM_API void om_mat4_rotate_y(float out[16], float f);
 OM_API void om_mat4_rotate_z(float out[16], float f);
 OM_API void om_mat4_mul(float out[16], const float a[16], const float b[16]);
 OM_API void om_mat4_fast_homogenous_inverse(float out[16], const float m[16]);
+
+/* BloomFilter::get_hash (utils.rs:93-107) and the shuffled 2x2 jitter table of
+ * render_thread.rs:164-174 (code bit1 = jitter i, bit0 = jitter j), as the library computes them. */
+OM_API uint64_t om_bloom_get_hash(uint64_t id);
+OM_API void om_jitter_table(uint32_t spp, uint64_t seed, uint8_t* out);
 
 /* Seeded scene generators (synthetic inputs for tests and benchmarks).  They
  * append to `s`.  Kinds:

@@ -26,6 +26,7 @@ RENDER_EXACT = 1 << 1
 RENDER_BRUTE_FORCE = 1 << 2
 RENDER_WAVEFRONT = 1 << 3
 RENDER_NO_SMEM_SCENE = 1 << 4
+RENDER_COUNTERS = 1 << 5
 
 CHUNK_PIXELS = 2730  # main.rs:174-175
 

@@ -1,0 +1,524 @@
+// Second half of om_api.cu: framebuffer kernels and the om_render handle.
+
+namespace {
+
+constexpr int UT = 256;  // threads of the small framebuffer kernels
+inline int ublocks(size_t n) { return int((n + UT - 1) / UT); }
+
+// utils.rs:12-17 + vec3.rs:73-76
+__device__ __forceinline__ uint32_t d_as_u8(float f) {
+    if (!(f == f) || f <= 0.f) return 0u;
+    if (f >= 255.f) return 255u;
+    return (uint32_t)f;
+}
+__device__ __forceinline__ uint32_t d_tone(float sum, float inv_n) { return d_as_u8(fminf(fmaxf(sqrtf(sum * inv_n), 0.f), 0.999f) * 256.0f); }
+__device__ __forceinline__ void d_color(float4 a, uint32_t c[3]) {
+    const uint32_t n = __float_as_uint(a.w);
+    if (n == 0u) { c[0] = c[1] = c[2] = 0u; return; }  // Stats::new
+    const float inv_n = 1.f / (float)n;                 // Div<f32> = multiply by the reciprocal
+    c[0] = d_tone(a.x, inv_n); c[1] = d_tone(a.y, inv_n); c[2] = d_tone(a.z, inv_n);
+}
+
+// Vec<Pixel> view of the accumulators (om_pixel, 40 bytes = 10 words)
+__global__ void k_pack_pixels(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t* __restrict__ out, uint32_t npx) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    const float4 a = acc[i];
+    const uint4 x = aux[i];
+    uint32_t c[3];
+    d_color(a, c);
+    uint32_t* o = out + 10u * i;
+    o[0] = __float_as_uint(a.x); o[1] = __float_as_uint(a.y); o[2] = __float_as_uint(a.z); o[3] = __float_as_uint(a.w);
+    o[4] = x.x; o[5] = x.y; o[6] = x.z; o[7] = x.w;
+    o[8] = c[0] | (c[1] << 8) | (c[2] << 16);
+    o[9] = 0u;
+}
+// MODE_NORMAL view, main.rs:374-381
+__global__ void k_rgb(const float4* __restrict__ acc, uint8_t* __restrict__ rgb, uint32_t npx) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    uint32_t c[3];
+    d_color(acc[i], c);
+    rgb[3u * i] = (uint8_t)c[0]; rgb[3u * i + 1] = (uint8_t)c[1]; rgb[3u * i + 2] = (uint8_t)c[2];
+}
+__global__ void k_export_accum(const float4* __restrict__ acc, const uint4* __restrict__ aux, float4* __restrict__ out, unsigned long long* __restrict__ bloom, uint32_t npx) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    const float4 a = acc[i];
+    const uint4 x = aux[i];
+    const float n = (float)__float_as_uint(a.w);
+    const float d = __uint_as_float(x.x);
+    out[2u * i] = make_float4(a.x, a.y, a.z, n);
+    out[2u * i + 1] = make_float4(n > 0.f ? n * d : 0.f, (float)x.y, 0.f, 0.f);
+    if (bloom) bloom[i] = ((unsigned long long)x.w << 32) | x.z;
+}
+__global__ void k_import_accum(float4* __restrict__ acc, uint4* __restrict__ aux, const float4* __restrict__ in, const unsigned long long* __restrict__ bloom, uint32_t npx) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    const float4 a = in[2u * i], b = in[2u * i + 1];
+    const uint32_t n = (uint32_t)(a.w + 0.5f);
+    acc[i] = make_float4(a.x, a.y, a.z, __uint_as_float(n));
+    uint4 x = aux[i];
+    x.x = __float_as_uint(n ? b.x / a.w : 0.f);
+    x.y = (uint32_t)(b.y + 0.5f);
+    if (bloom) { x.z = (uint32_t)bloom[i]; x.w = (uint32_t)(bloom[i] >> 32); }
+    aux[i] = x;
+}
+__global__ void k_bloom_or(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, uint32_t nsrc, size_t n) {
+    const size_t i = (size_t)blockIdx.x * UT + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long v = dst[i];
+    for (uint32_t k = 0; k < nsrc; k++) v |= src[(size_t)k * n + i];
+    dst[i] = v;
+}
+// ThreadPixels::add_run / swap_buffers (render_thread.rs:92-101) for the whole image: the list
+// of pixels that still want samples, by warp ballot + popc and one atomic per warp.
+__global__ void k_compact_live(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t npx, uint32_t budget, uint32_t adaptive,
+                               uint32_t part_rank, uint32_t part_world, uint32_t* __restrict__ list, uint32_t* __restrict__ count) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    bool live = false;
+    if (i < npx) {
+        const bool mine = part_world <= 1u || ((i / OM_CHUNK_PIXELS) % part_world) == part_rank;
+        const uint32_t n = __float_as_uint(acc[i].w);
+        live = mine && n < budget && !(adaptive && aux[i].y >= 5u);
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, live);
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t base = 0;
+    if (lane == 0u && m) base = atomicAdd(count, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (live) list[base + __popc(m & ((1u << lane) - 1u))] = i;
+}
+// dependent-free FMA chains: the FP32 roofline denominator
+__global__ void k_fma_peak(float* out, int iters) {
+    float a[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = 1.0f + 0.001f * (float)(threadIdx.x + k);
+    const float m = 0.9999f, c = 0.0001f;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = fmaf(a[k], m, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += a[k];
+    if (s == 12345.678f) out[0] = s;
+}
+
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+};
+
+}  // namespace
+
+struct om_render {
+    om_scene* scene = nullptr;
+    om_camera cam;
+    om_render_params p;
+    int dev = 0;
+    DeviceProps props;
+    DevScene ds;
+    uint32_t npx = 0, budget = 0;
+    cudaStream_t stream = nullptr;      // the stream work is issued on
+    cudaStream_t own_stream = nullptr;  // created by the handle
+    float4* acc = nullptr;
+    uint4* aux = nullptr;
+    uint8_t* jitter = nullptr;
+    unsigned long long* counters = nullptr;
+    uint32_t* live_list = nullptr;
+    uint32_t* live_count = nullptr;
+    bool have_live = false;
+    void* staging = nullptr;  // device staging for read-outs
+    size_t staging_bytes = 0;
+    std::vector<EventPair> pending, pool;
+    float acc_ms = 0.f;
+    uint32_t launches = 0;
+    bool use_smem = false;
+    size_t smem_bytes = 0;
+    int grid = 0;
+};
+
+namespace {
+om_status ensure_staging(om_render* r, size_t bytes) {
+    if (r->staging_bytes >= bytes) return OM_OK;
+    if (r->staging) cudaFree(r->staging);
+    r->staging = nullptr;
+    r->staging_bytes = 0;
+    CU(cudaMalloc(&r->staging, bytes));
+    r->staging_bytes = bytes;
+    return OM_OK;
+}
+omk::RenderArgs make_args(const om_render* r) {
+    omk::RenderArgs a;
+    memset(&a, 0, sizeof a);
+    a.scene = r->scene->fz.hdr;
+    a.hot_g = r->ds.hot;
+    a.cold_g = r->ds.cold;
+    a.cam = r->cam;
+    a.width = r->p.width; a.height = r->p.height; a.npx = r->npx;
+    a.spp_budget = r->budget;
+    a.sample_base = r->p.sample_base;
+    a.max_depth = r->p.max_depth;
+    a.tmin = r->p.tmin; a.tmax = r->p.tmax;
+    a.seed_lo = uint32_t(r->p.seed); a.seed_hi = uint32_t(r->p.seed >> 32);
+    a.flags = r->p.flags;
+    a.part_rank = r->p.part_rank; a.part_world = r->p.part_world ? r->p.part_world : 1u;
+    if (a.part_world > 1u) {
+        const uint32_t chunks = (r->npx + OM_CHUNK_PIXELS - 1) / OM_CHUNK_PIXELS;
+        const uint32_t mine = (chunks + a.part_world - 1 - a.part_rank) / a.part_world;
+        a.n_work = mine * OM_CHUNK_PIXELS;
+        a.tiles_x = 0;
+    } else {
+        a.tiles_x = (r->p.width + 7u) / 8u;
+        a.n_work = a.tiles_x * ((r->p.height + 3u) / 4u) * 32u;
+    }
+    a.jitter = r->jitter;
+    a.acc = r->acc; a.aux = r->aux;
+    a.counters = r->counters;
+    return a;
+}
+om_status drain_events(om_render* r) {
+    for (EventPair& e : r->pending) {
+        CU(cudaEventSynchronize(e.b));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e.a, e.b));
+        r->acc_ms += ms;
+        r->pool.push_back(e);
+    }
+    r->pending.clear();
+    return OM_OK;
+}
+}  // namespace
+
+extern "C" {
+
+uint64_t om_bloom_get_hash(uint64_t id) { return omh::bloom_get_hash(id); }
+void om_jitter_table(uint32_t spp, uint64_t seed, uint8_t* out) {
+    std::vector<uint8_t> t;
+    omh::jitter_table(spp, seed, t);
+    if (spp) memcpy(out, t.data(), spp);
+}
+
+om_status om_render_destroy(om_render* r) {
+    if (!r) return OM_OK;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(r->dev);
+    if (r->stream) cudaStreamSynchronize(r->stream);
+    for (EventPair& e : r->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    for (EventPair& e : r->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    cudaFree(r->acc); cudaFree(r->aux); cudaFree(r->jitter); cudaFree(r->counters); cudaFree(r->live_list); cudaFree(r->live_count); cudaFree(r->staging);
+    if (r->own_stream) cudaStreamDestroy(r->own_stream);
+    cudaSetDevice(prev);
+    delete r;
+    return OM_OK;
+}
+
+om_status om_render_create(om_render** out, const om_scene* frozen, const om_camera* cam, const om_render_params* params) {
+    if (!out || !frozen || !cam || !params) return fail(OM_ERR_INVALID, "om_render_create: NULL argument");
+    *out = nullptr;
+    if (!frozen->frozen) return fail(OM_ERR_INVALID, "om_render_create: scene is not frozen (om_scene_freeze)");
+    const om_render_params& p = *params;
+    if (p.width < 2 || p.height < 2) return fail(OM_ERR_INVALID, "om_render_create: image must be at least 2x2 (u,v divide by W-1,H-1; render_thread.rs:190-191)");
+    if (uint64_t(p.width) * p.height > 0x7FFFFFFFull) return fail(OM_ERR_INVALID, "om_render_create: image too large");
+    if (p.spp_max == 0) return fail(OM_ERR_INVALID, "om_render_create: spp_max is 0");
+    if (p.sample_base >= p.spp_max || uint64_t(p.sample_base) + p.sample_count > p.spp_max) return fail(OM_ERR_INVALID, "om_render_create: sample slice outside [0, spp_max)");
+    if (p.part_world > 1 && p.part_rank >= p.part_world) return fail(OM_ERR_INVALID, "om_render_create: part_rank >= part_world");
+    if ((p.flags & OM_RENDER_ADAPTIVE) && (p.sample_base != 0 || (p.sample_count != 0 && p.sample_count != p.spp_max)))
+        return fail(OM_ERR_INVALID, "om_render_create: adaptive retirement needs all of a pixel's samples in order; use the chunk partition, not an spp slice");
+    if (p.flags & OM_RENDER_WAVEFRONT) return fail(OM_ERR_UNSUPPORTED, "om_render_create: the wavefront pipeline is not built yet");
+    int dev = 0;
+    om_status st = pick_device(p.device, dev);
+    if (st != OM_OK) return st;
+    om_render* r = new (std::nothrow) om_render();
+    if (!r) return fail(OM_ERR_OOM, "om_render_create: out of host memory");
+    r->scene = const_cast<om_scene*>(frozen);
+    r->cam = *cam;
+    r->p = p;
+    r->dev = dev;
+    r->npx = p.width * p.height;
+    r->budget = p.sample_count ? p.sample_count : (p.spp_max - p.sample_base);
+#define OM_TRY(call)                                 \
+    do {                                             \
+        om_status s_ = (call);                       \
+        if (s_ != OM_OK) { std::string keep = g_err; om_render_destroy(r); g_err = keep; return s_; } \
+    } while (0)
+    auto body = [&]() -> om_status {
+        CU(cudaSetDevice(dev));
+        om_status s2 = device_props(dev, r->props);
+        if (s2 != OM_OK) return s2;
+        s2 = scene_on_device(r->scene, dev, r->ds);
+        if (s2 != OM_OK) return s2;
+        CU(cudaStreamCreateWithFlags(&r->own_stream, cudaStreamNonBlocking));
+        r->stream = r->own_stream;
+        CU(cudaMalloc(&r->acc, size_t(r->npx) * sizeof(float4)));
+        CU(cudaMalloc(&r->aux, size_t(r->npx) * sizeof(uint4)));
+        CU(cudaMalloc(&r->jitter, p.spp_max));
+        CU(cudaMalloc(&r->counters, omk::ctr::CTR_COUNT * sizeof(unsigned long long)));
+        CU(cudaMemsetAsync(r->acc, 0, size_t(r->npx) * sizeof(float4), r->stream));
+        CU(cudaMemsetAsync(r->aux, 0, size_t(r->npx) * sizeof(uint4), r->stream));
+        CU(cudaMemsetAsync(r->counters, 0, omk::ctr::CTR_COUNT * sizeof(unsigned long long), r->stream));
+        std::vector<uint8_t> jt;
+        omh::jitter_table(p.spp_max, p.seed, jt);
+        CU(cudaMemcpyAsync(r->jitter, jt.data(), p.spp_max, cudaMemcpyHostToDevice, r->stream));
+        CU(cudaStreamSynchronize(r->stream));
+        if (p.flags & OM_RENDER_ADAPTIVE) {
+            CU(cudaMalloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t)));
+            CU(cudaMalloc(&r->live_count, sizeof(uint32_t)));
+        }
+        // launch shape: persistent grid, hot image in shared memory when two CTAs still fit per SM
+        const bool exact = (p.flags & OM_RENDER_EXACT) != 0, count = (p.flags & OM_RENDER_COUNTERS) != 0;
+        const size_t hot_bytes = size_t(r->scene->fz.hdr.hot_units) * 16u;
+        r->use_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= r->props.smem_optin / 2;
+        r->smem_bytes = r->use_smem ? hot_bytes : 0;
+        int occ = exact ? om_exact::render_occupancy(r->use_smem, count, r->smem_bytes) : om_fast::render_occupancy(r->use_smem, count, r->smem_bytes);
+        if (occ < 1) {
+            cudaError_t e = cudaGetLastError();
+            return fail(OM_ERR_CUDA, "render kernel cannot be resident on device %d (%s)", dev, cudaGetErrorString(e));
+        }
+        r->grid = occ * r->props.sms;
+        return OM_OK;
+    };
+    OM_TRY(body());
+#undef OM_TRY
+    *out = r;
+    return OM_OK;
+}
+
+om_status om_render_set_stream(om_render* r, void* cuda_stream) {
+    if (!r) return fail(OM_ERR_INVALID, "om_render_set_stream: NULL handle");
+    CU(cudaSetDevice(r->dev));
+    CU(cudaStreamSynchronize(r->stream));
+    om_status s = drain_events(r);
+    if (s != OM_OK) return s;
+    r->stream = cuda_stream ? (cudaStream_t)cuda_stream : r->own_stream;
+    return OM_OK;
+}
+
+om_status om_render_reset(om_render* r) {
+    if (!r) return fail(OM_ERR_INVALID, "om_render_reset: NULL handle");
+    CU(cudaSetDevice(r->dev));
+    CU(cudaMemsetAsync(r->acc, 0, size_t(r->npx) * sizeof(float4), r->stream));
+    CU(cudaMemsetAsync(r->aux, 0, size_t(r->npx) * sizeof(uint4), r->stream));
+    CU(cudaMemsetAsync(r->counters, 0, omk::ctr::CTR_COUNT * sizeof(unsigned long long), r->stream));
+    r->have_live = false;
+    return OM_OK;
+}
+
+om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
+    if (!r) return fail(OM_ERR_INVALID, "om_render_launch: NULL handle");
+    CU(cudaSetDevice(r->dev));
+    omk::RenderArgs a = make_args(r);
+    a.spp_pass = spp_this_pass ? spp_this_pass : r->budget;
+    const bool adaptive = (r->p.flags & OM_RENDER_ADAPTIVE) != 0;
+    if (adaptive && r->have_live) { a.live_list = r->live_list; a.live_count = r->live_count; }
+    EventPair ev;
+    if (!r->pool.empty()) { ev = r->pool.back(); r->pool.pop_back(); }
+    else { CU(cudaEventCreate(&ev.a)); CU(cudaEventCreate(&ev.b)); }
+    CU(cudaMemsetAsync(r->counters + omk::ctr::CTR_TICKET, 0, sizeof(unsigned long long), r->stream));
+    CU(cudaEventRecord(ev.a, r->stream));
+    const bool exact = (r->p.flags & OM_RENDER_EXACT) != 0, count = (r->p.flags & OM_RENDER_COUNTERS) != 0;
+    cudaError_t e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
+                          : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+    if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
+    if (adaptive) {  // next pass walks only the pixels that still want samples
+        CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
+        k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, r->live_list, r->live_count);
+        CU(cudaGetLastError());
+        r->have_live = true;
+    }
+    CU(cudaEventRecord(ev.b, r->stream));
+    r->pending.push_back(ev);
+    r->launches++;
+    return OM_OK;
+}
+
+om_status om_render_sync(om_render* r) {
+    if (!r) return fail(OM_ERR_INVALID, "om_render_sync: NULL handle");
+    CU(cudaSetDevice(r->dev));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+static om_status read_counter(om_render* r, int slot, uint64_t* out) {
+    if (!r || !out) return fail(OM_ERR_INVALID, "counter read: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    unsigned long long v = 0;
+    CU(cudaMemcpyAsync(&v, r->counters + slot, sizeof v, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    *out = v;
+    return OM_OK;
+}
+om_status om_render_samples_done(om_render* r, uint64_t* credited) { return read_counter(r, omk::ctr::CTR_CREDITED, credited); }
+om_status om_render_samples_traced(om_render* r, uint64_t* traced) { return read_counter(r, omk::ctr::CTR_TRACED, traced); }
+om_status om_render_perf_counters(om_render* r, uint64_t out[16]) {
+    if (!r || !out) return fail(OM_ERR_INVALID, "om_render_perf_counters: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    CU(cudaMemcpyAsync(out, r->counters, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+om_status om_render_elapsed_ms(om_render* r, float* ms, uint32_t* launches) {
+    if (!r) return fail(OM_ERR_INVALID, "om_render_elapsed_ms: NULL handle");
+    CU(cudaSetDevice(r->dev));
+    om_status s = drain_events(r);
+    if (s != OM_OK) return s;
+    if (ms) *ms = r->acc_ms;
+    if (launches) *launches = r->launches;
+    r->acc_ms = 0.f;
+    r->launches = 0;
+    return OM_OK;
+}
+
+om_status om_render_read_pixels(om_render* r, om_pixel* host, size_t n) {
+    if (!r || !host) return fail(OM_ERR_INVALID, "om_render_read_pixels: NULL argument");
+    if (n != r->npx) return fail(OM_ERR_INVALID, "om_render_read_pixels: n must be width*height");
+    static_assert(sizeof(om_pixel) == 40, "om_pixel layout");
+    CU(cudaSetDevice(r->dev));
+    om_status s = ensure_staging(r, n * sizeof(om_pixel));
+    if (s != OM_OK) return s;
+    k_pack_pixels<<<ublocks(n), UT, 0, r->stream>>>(r->acc, r->aux, (uint32_t*)r->staging, r->npx);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(host, r->staging, n * sizeof(om_pixel), cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+om_status om_render_read_rgb(om_render* r, uint8_t* host_rgb, size_t nbytes) {
+    if (!r || !host_rgb) return fail(OM_ERR_INVALID, "om_render_read_rgb: NULL argument");
+    if (nbytes != size_t(r->npx) * 3u) return fail(OM_ERR_INVALID, "om_render_read_rgb: nbytes must be width*height*3");
+    CU(cudaSetDevice(r->dev));
+    om_status s = ensure_staging(r, nbytes);
+    if (s != OM_OK) return s;
+    k_rgb<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, (uint8_t*)r->staging, r->npx);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(host_rgb, r->staging, nbytes, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+
+om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_index, uint64_t* ids, float* t, size_t n) {
+    if (!r || !ids || !t) return fail(OM_ERR_INVALID, "om_render_primary: NULL argument");
+    if (n != r->npx) return fail(OM_ERR_INVALID, "om_render_primary: n must be width*height");
+    if (mode > 1 || (mode == 1 && sample_index >= r->p.spp_max)) return fail(OM_ERR_INVALID, "om_render_primary: bad mode / sample index");
+    CU(cudaSetDevice(r->dev));
+    om_status s = ensure_staging(r, n * 12u);
+    if (s != OM_OK) return s;
+    unsigned long long* d_ids = (unsigned long long*)r->staging;
+    float* d_t = (float*)(d_ids + n);
+    omk::RenderArgs a = make_args(r);
+    const int grid = std::min(ublocks(n), r->props.sms * 8);
+    cudaError_t e = (r->p.flags & OM_RENDER_EXACT) ? om_exact::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t)
+                                                   : om_fast::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t);
+    if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_primary launch failed: %s", cudaGetErrorString(e));
+    CU(cudaMemcpyAsync(ids, d_ids, n * 8u, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaMemcpyAsync(t, d_t, n * 4u, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+
+om_status om_render_export_accum(om_render* r, float* dev_acc, uint64_t* dev_bloom) {
+    if (!r || !dev_acc) return fail(OM_ERR_INVALID, "om_render_export_accum: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    k_export_accum<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, (float4*)dev_acc, (unsigned long long*)dev_bloom, r->npx);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+om_status om_render_import_accum(om_render* r, const float* dev_acc, const uint64_t* dev_bloom) {
+    if (!r || !dev_acc) return fail(OM_ERR_INVALID, "om_render_import_accum: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    k_import_accum<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, (const float4*)dev_acc, (const unsigned long long*)dev_bloom, r->npx);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+om_status om_bloom_or(uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc, size_t n, int32_t device) {
+    if (!dev_dst || (!dev_src && nsrc)) return fail(OM_ERR_INVALID, "om_bloom_or: NULL argument");
+    int dev = 0;
+    om_status s = pick_device(device, dev);
+    if (s != OM_OK) return s;
+    CU(cudaSetDevice(dev));
+    k_bloom_or<<<ublocks(n), UT>>>((unsigned long long*)dev_dst, (const unsigned long long*)dev_src, (uint32_t)nsrc, n);
+    CU(cudaGetLastError());
+    CU(cudaDeviceSynchronize());
+    return OM_OK;
+}
+
+om_status om_trace_rays(const om_scene* frozen, const float* origins, const float* dirs, size_t n, float tmin, float tmax, uint32_t flags, int32_t device,
+                        uint64_t* ids, float* t, float* points, float* normals) {
+    if (!frozen || !frozen->frozen) return fail(OM_ERR_INVALID, "om_trace_rays: scene is not frozen");
+    if ((!origins || !dirs) && n) return fail(OM_ERR_INVALID, "om_trace_rays: NULL rays");
+    if (n > 0x7FFFFFFFull / 3) return fail(OM_ERR_INVALID, "om_trace_rays: too many rays");
+    int dev = 0;
+    om_status s = pick_device(device, dev);
+    if (s != OM_OK) return s;
+    if (n == 0) return OM_OK;
+    CU(cudaSetDevice(dev));
+    DeviceProps props;
+    s = device_props(dev, props);
+    if (s != OM_OK) return s;
+    DevScene ds;
+    s = scene_on_device(const_cast<om_scene*>(frozen), dev, ds);
+    if (s != OM_OK) return s;
+    char* buf = nullptr;
+    const size_t b_rays = n * 12u, b_ids = n * 8u, b_t = n * 4u;
+    CU(cudaMalloc(&buf, 2 * b_rays + b_ids + b_t + 2 * b_rays));
+    omk::TraceArgs a;
+    memset(&a, 0, sizeof a);
+    a.scene = frozen->fz.hdr; a.hot_g = ds.hot; a.cold_g = ds.cold;
+    a.ids = (unsigned long long*)buf;
+    float* d_o = (float*)(buf + b_ids);
+    float* d_d = d_o + 3 * n;
+    a.origins = d_o; a.dirs = d_d;
+    a.t = d_d + 3 * n;
+    a.points = a.t + n;
+    a.normals = a.points + 3 * n;
+    a.n = (uint32_t)n; a.tmin = tmin; a.tmax = tmax; a.flags = flags;
+    auto done = [&](om_status st) { cudaFree(buf); return st; };
+    cudaError_t e = cudaMemcpy(d_o, origins, b_rays, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_d, dirs, b_rays, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "om_trace_rays: upload failed: %s", cudaGetErrorString(e)));
+    const size_t hot_bytes = size_t(frozen->fz.hdr.hot_units) * 16u;
+    const bool smem = !(flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= props.smem_optin / 2;
+    const int grid = std::min(ublocks(n), props.sms * 8);
+    e = (flags & OM_RENDER_EXACT) ? om_exact::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0) : om_fast::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "k_trace_rays failed: %s", cudaGetErrorString(e)));
+    if (ids) e = cudaMemcpy(ids, a.ids, b_ids, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && t) e = cudaMemcpy(t, a.t, b_t, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && points) e = cudaMemcpy(points, a.points, b_rays, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && normals) e = cudaMemcpy(normals, a.normals, b_rays, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "om_trace_rays: download failed: %s", cudaGetErrorString(e)));
+    return done(OM_OK);
+}
+
+om_status om_bench_fp32_peak(int32_t device, float* tflops, float* ms_out) {
+    int dev = 0;
+    om_status s = pick_device(device, dev);
+    if (s != OM_OK) return s;
+    CU(cudaSetDevice(dev));
+    DeviceProps props;
+    s = device_props(dev, props);
+    if (s != OM_OK) return s;
+    float* d = nullptr;
+    CU(cudaMalloc(&d, 4));
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+    const int iters = 1 << 16, grid = props.sms * 8, threads = 256;
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        CU(cudaEventRecord(a));
+        k_fma_peak<<<grid, threads>>>(d, iters);
+        CU(cudaEventRecord(b));
+        CU(cudaEventSynchronize(b));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, a, b));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
+    const double flops = 2.0 * 8.0 * double(iters) * double(grid) * double(threads);
+    if (tflops) *tflops = float(flops / (double(best) * 1e-3) / 1e12);
+    if (ms_out) *ms_out = best;
+    return OM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,36 @@
+// Flattened BVH over the traced primitives' world bounding boxes.  The reference has no BVH: it
+// has Bounded::build_world_bounding_box (bounding_box.rs:69-73; traced.rs:65-70,208-219,301-304)
+// feeding a screen-space grid for primary rays only (camera_hash.rs) and a linear scan for every
+// other ray (hits.rs:270-286).  This builder takes the same per-object world AABBs (tightened:
+// exact ellipsoid extents, the cube's real +-0.5 corners, the triangle/parallelogram vertices)
+// and produces a binary tree that serves every ray.
+#pragma once
+#include <stdint.h>
+
+#include <vector>
+
+namespace omb {
+
+struct Aabb {
+    float lo[3], hi[3];
+};
+
+// 64-byte node: both children's boxes + child references (one shared-memory fetch per visit).
+// child >= 0: index of an inner node; child < 0: leaf, ~child is the primitive reference
+// (prim type code << 28 | index).  An empty child has an inverted box and is never entered.
+struct alignas(16) Node {
+    float lmin[3], lmax[3], rmin[3], rmax[3];
+    int32_t left, right;
+    uint32_t pad0, pad1;
+};
+static_assert(sizeof(Node) == 64, "node must be 64 bytes");
+
+struct BuildResult {
+    std::vector<Node> nodes;  // nodes[0] is the root when !nodes.empty()
+    uint32_t depth = 0;
+};
+
+// refs[i] / boxes[i] describe primitive i.  Binned SAH, one primitive per leaf.
+void build(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, BuildResult& out);
+
+}  // namespace omb

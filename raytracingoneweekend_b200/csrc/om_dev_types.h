@@ -1,0 +1,53 @@
+// Layout of the frozen scene as the kernels see it.  Shared by the host packer (om_scene.cpp)
+// and the device code (om_device.cuh).  Everything is addressed in 16-byte units so that every
+// access is one LDS.128 / LDG.128.
+//
+//  hot image  (staged into shared memory by TMA bulk copy when it fits; else read from global/L2)
+//      BVH nodes 64 B | sphere world->local rows 48 B | cube world->local rows 48 B |
+//      triangle 64 B | infinite plane 32 B | parallelogram 64 B | always-test refs 4 B |
+//      marched sphere 16 B | marched box 32 B | marched torus 144 B
+//  cold image (global memory; touched once per hit, not per test)
+//      sphere local->world rows 48 B | cube local->world rows 48 B | material+bloom 32 B per object
+#pragma once
+#include <stdint.h>
+
+namespace omd {
+
+// primitive type codes in the reference's scan order (hits.rs:370-371): on equal t the LATER
+// object of the linear scan wins (`root > t_max` rejects only strictly larger roots,
+// traced.rs:51,108,178,282), so a larger ref beats a smaller one.
+enum : uint32_t { PT_SPHERE = 0, PT_CUBE = 1, PT_TRI = 2, PT_PLANE = 3, PT_PARA = 4, PT_MSPHERE = 5, PT_MBOX = 6, PT_MTORUS = 7 };
+constexpr uint32_t REF_NONE = 0xFFFFFFFFu;
+#if defined(__CUDACC__)
+#define OMD_HD __host__ __device__ __forceinline__
+#else
+#define OMD_HD inline
+#endif
+OMD_HD uint32_t make_ref(uint32_t type, uint32_t index) { return (type << 28) | index; }
+OMD_HD uint32_t ref_type(uint32_t ref) { return ref >> 28; }
+OMD_HD uint32_t ref_index(uint32_t ref) { return ref & 0x0FFFFFFFu; }
+
+// sizes in 16-byte units
+constexpr uint32_t U_NODE = 4, U_XF = 3, U_BARY = 4, U_PLANE = 2, U_MSPHERE = 1, U_MBOX = 2, U_MTORUS = 9, U_MAT = 2;
+
+struct SceneHeader {
+    uint32_t n[8];         // object count per PT_* type
+    uint32_t n_nodes;      // BVH inner nodes (0 = no BVH primitives)
+    uint32_t n_large;      // refs in the always-test list (infinite planes, scene-sized objects)
+    uint32_t n_bvh_prims;  // primitives reachable through the BVH
+    uint32_t bvh_depth;
+    // hot image offsets, 16-byte units
+    uint32_t off_nodes, off_hot[8], off_large;
+    uint32_t hot_units;    // total size of the hot image
+    // cold image offsets, 16-byte units
+    uint32_t off_sph_l2w, off_cube_l2w, off_mat;
+    uint32_t mat_base[8];  // first material record of each type
+    uint32_t cold_units;
+    // padded union of the marched objects' bounds: a ray that misses it cannot hit a marched
+    // object and cannot start inside one.  lo > hi when the scene has no marched object.
+    float march_lo[3], march_hi[3];
+    uint32_t n_marched;
+    uint32_t pad;
+};
+
+}  // namespace omd

@@ -1,0 +1,838 @@
+// Device code of the B200 renderer: everything under render_thread::render
+// (reference src/render_thread.rs:145-202) as CUDA for sm_100a.
+//
+// This header is compiled twice, into two namespaces:
+//   om_exact  (om_kernels_exact.cu, nvcc -fmad=false): no FMA contraction, IEEE div/sqrt, the
+//             reference's operation order -> bit-identical to the CPU oracle, sample by sample.
+//   om_fast   (om_kernels_fast.cu): the same expressions with FMA contraction.
+// OM_NS and OM_EXACT are set by the including .cu file.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ottomarcher.h"
+#include "om_args.h"
+#include "om_dev_types.h"
+#include "om_math.h"
+
+#ifndef OM_EXACT
+#error "include from om_kernels_exact.cu / om_kernels_fast.cu"
+#endif
+
+namespace OM_NS {
+
+using om::V3;
+using om::v3;
+using omd::SceneHeader;
+
+constexpr bool kExact = (OM_EXACT != 0);
+constexpr float kInf = __builtin_huge_valf();
+constexpr float HIT_SIZE = 0.001f;  // hits.rs:113
+constexpr int UNSTUCK_MAX_STEPS = 1 << 20;
+constexpr int CTA_THREADS = 256;
+
+using omk::RenderArgs;
+using omk::TraceArgs;
+using namespace omk::ctr;
+
+// ============================================================================================
+// Philox4x32-10 counter RNG: key = seed, counter = (block, pixel, sample, stream).  Replaces
+// rand::thread_rng (utils.rs:24-27).  Same contract as omh::Rng / the oracle's ref::Rng.
+// ============================================================================================
+struct Rng {
+    uint32_t k0, k1, a, b, draw;
+    uint32_t b0, b1, b2, b3;
+};
+__device__ __forceinline__ void philox_block(Rng& g) {
+    uint32_t c0 = g.draw >> 2, c1 = g.a, c2 = g.b, c3 = 0u /* STREAM_PATH */, k0 = g.k0, k1 = g.k1;
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        const uint32_t lo0 = 0xD2511F53u * c0, hi0 = __umulhi(0xD2511F53u, c0);
+        const uint32_t lo1 = 0xCD9E8D57u * c2, hi1 = __umulhi(0xCD9E8D57u, c2);
+        c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    g.b0 = c0; g.b1 = c1; g.b2 = c2; g.b3 = c3;
+}
+__device__ __forceinline__ void rng_init(Rng& g, uint32_t k0, uint32_t k1, uint32_t pixel, uint32_t sample) {
+    g.k0 = k0; g.k1 = k1; g.a = pixel; g.b = sample; g.draw = 0;
+}
+__device__ __forceinline__ float rng_f32(Rng& g) {  // utils.rs:25: uniform [0,1), 24 bits
+    const uint32_t lane = g.draw & 3u;
+    if (lane == 0u) philox_block(g);
+    g.draw++;
+    const uint32_t u = lane == 0u ? g.b0 : (lane == 1u ? g.b1 : (lane == 2u ? g.b2 : g.b3));
+    return (float)(u >> 8) * 5.9604644775390625e-8f;
+}
+__device__ __forceinline__ float rng_range(Rng& g, float mn, float mx) { return rng_f32(g) * (mx - mn) + mn; }  // utils.rs:26
+__device__ __forceinline__ V3 rand_in_unit_sphere(Rng& g) {  // vec3.rs:92-97
+    for (;;) {
+        const float x = rng_range(g, -1.f, 1.f), y = rng_range(g, -1.f, 1.f), z = rng_range(g, -1.f, 1.f);
+        const V3 p = v3(x, y, z);
+        if (om::length_squared(p) < 1.f) return p;
+    }
+}
+__device__ __forceinline__ V3 rand_in_unit_disc(Rng& g) {  // vec3.rs:108-113
+    for (;;) {
+        const float x = rng_range(g, -1.f, 1.f), y = rng_range(g, -1.f, 1.f);
+        const V3 p = v3(x, y, 0.f);
+        if (om::length_squared(p) < 1.f) return p;
+    }
+}
+
+// ============================================================================================
+// scene access: hot image in shared memory (SMEM) or global memory; cold image in global
+// ============================================================================================
+extern __shared__ float4 om_smem[];
+
+template <bool SMEM>
+struct SceneView {
+    const float4* hot_g;
+    const float4* cold_g;
+    __device__ __forceinline__ float4 hot(uint32_t u) const {
+        if (SMEM) return om_smem[u];
+        return __ldg(hot_g + u);
+    }
+    __device__ __forceinline__ float4 cold(uint32_t u) const { return __ldg(cold_g + u); }
+};
+
+struct Ray {
+    V3 o, d;
+};
+__device__ __forceinline__ V3 ray_at(const Ray& r, float t) { return r.o + t * r.d; }  // ray.rs:14-16
+
+// Mat4x4::dot_p3 / dot_v3 over the three stored rows (mat4x4.rs:49-57)
+__device__ __forceinline__ V3 xf_point(float4 r0, float4 r1, float4 r2, V3 p) {
+    return v3(r0.x * p.x + r0.y * p.y + r0.z * p.z + r0.w, r1.x * p.x + r1.y * p.y + r1.z * p.z + r1.w, r2.x * p.x + r2.y * p.y + r2.z * p.z + r2.w);
+}
+__device__ __forceinline__ V3 xf_vec(float4 r0, float4 r1, float4 r2, V3 p) {
+    if (kExact)  // the reference multiplies the translation column by w = 0 and adds it
+        return v3(r0.x * p.x + r0.y * p.y + r0.z * p.z + r0.w * 0.f, r1.x * p.x + r1.y * p.y + r1.z * p.z + r1.w * 0.f, r2.x * p.x + r2.y * p.y + r2.z * p.z + r2.w * 0.f);
+    return v3(r0.x * p.x + r0.y * p.y + r0.z * p.z, r1.x * p.x + r1.y * p.y + r1.z * p.z, r2.x * p.x + r2.y * p.y + r2.z * p.z);
+}
+
+// ---- traced primitives: parametric distance only (the hit record is built once, for the winner) --
+// Sphere::hit traced.rs:38-56
+__device__ __forceinline__ bool sphere_t(float4 r0, float4 r1, float4 r2, const Ray& r, float t_min, float t_max, float& t_out) {
+    const V3 ol = xf_point(r0, r1, r2, r.o), dl = xf_vec(r0, r1, r2, r.d);
+    const float a = om::length_squared(dl);
+    const float half_b = om::dot(ol, dl);
+    const float c = om::length_squared(ol) - 1.f;
+    const float discriminant = half_b * half_b - a * c;
+    if (discriminant < 0.f) return false;
+    const float sqrtd = sqrtf(discriminant);
+    float root = (-half_b - sqrtd) / a;
+    if (root < t_min || root > t_max) {
+        root = (-half_b + sqrtd) / a;
+        if (root < t_min || root > t_max) return false;
+    }
+    t_out = root;
+    return true;
+}
+// ray_plane_intersect traced.rs:91-99
+__device__ __forceinline__ void ray_plane(const Ray& r, V3 n, V3 c, float& t, float& div) {
+    div = om::dot(n, r.d);
+    if (fabsf(div) < 0.000001f) { t = kInf; div = 0.f; return; }
+    const float num = -om::dot(n, r.o - c);
+    t = num / div;
+}
+__device__ __forceinline__ bool plane_t(float4 pn, float4 pc, const Ray& r, float t_min, float t_max, float& t_out) {  // traced.rs:105-110
+    float root, ndd;
+    ray_plane(r, v3(pn.x, pn.y, pn.z), v3(pc.x, pc.y, pc.z), root, ndd);
+    if (root == kInf || root < t_min || root > t_max) return false;
+    t_out = root;
+    return true;
+}
+// Barycentric::hit_aux traced.rs:176-197;  a = (origin, u_length) b = (uxv, v_length)
+// c = (base_inv row 0, v_in_base.x) d = (base_inv row 2, v_in_base.z)
+__device__ __forceinline__ bool bary_t(float4 a, float4 b, float4 c, float4 d, bool triangle, const Ray& r, float t_min, float t_max, float& t_out) {
+    float root, ndd;
+    const V3 origin = v3(a.x, a.y, a.z);
+    ray_plane(r, v3(b.x, b.y, b.z), origin, root, ndd);
+    if (root == kInf || root < t_min || root > t_max) return false;
+    const V3 pfo = ray_at(r, root) - origin;
+    const float rx = om::dot(v3(c.x, c.y, c.z), pfo), ry = om::dot(v3(d.x, d.y, d.z), pfo);
+    const float ux = 1.f, uy = 0.f, vx = c.w, vy = d.w;
+    const float det = ux * vy - vx * uy;
+    const float lambda1 = ((rx * vy - vx * ry) / det) / a.w;
+    const float lambda2 = (-(rx * uy - ux * ry) / det) / b.w;
+    const float lambda3 = 1.f - lambda1 - lambda2;
+    bool ok = lambda1 > 0.f && lambda2 > 0.f && lambda1 < 1.f && lambda2 < 1.f;
+    if (triangle) ok = ok && lambda3 > 0.f && lambda3 < 1.f;
+    if (!ok) return false;
+    t_out = root;
+    return true;
+}
+// Cube::hit traced.rs:265-289; also returns the face axis
+__device__ __forceinline__ bool cube_t(float4 r0, float4 r1, float4 r2, const Ray& r, float t_min, float t_max, float& t_out, int& axis_out) {
+    Ray lr;
+    lr.o = xf_point(r0, r1, r2, r.o);
+    lr.d = xf_vec(r0, r1, r2, r.d);
+    float smallest_t = kInf;
+    int idx = -1;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        const float di = om::comp(lr.d, i), oi = om::comp(lr.o, i);
+        if (fabsf(di) < 0.00001f) continue;
+        const float t1 = (0.5f - oi) / di;
+        const float t2 = (-0.5f - oi) / di;
+        const float t = (t1 >= 0.f && t2 >= 0.f) ? fminf(t1, t2) : fmaxf(t1, t2);
+        if (t > smallest_t || t > t_max || t < t_min) continue;
+        const float f = om::max_val(om::vabs(ray_at(lr, t)));
+        if (!(fabsf(f - 0.5f) <= 0.00001f)) continue;
+        smallest_t = t;
+        idx = i;
+    }
+    if (idx < 0) return false;
+    t_out = smallest_t;
+    axis_out = idx;
+    return true;
+}
+
+// ---- closest hit over the traced primitives ------------------------------------------------
+struct Best {
+    float t;
+    uint32_t ref;
+};
+// Linear scan keeps the LATER object on equal t (see om_dev_types.h); any visiting order gives
+// the same winner with this rule.
+__device__ __forceinline__ void accept(Best& b, float t, uint32_t ref) {
+    if (t < b.t || b.ref == omd::REF_NONE || ref > b.ref) { b.t = t; b.ref = ref; }
+}
+template <bool SMEM>
+__device__ __forceinline__ void test_prim(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t ref, const Ray& r, float t_min, Best& best) {
+    const uint32_t type = omd::ref_type(ref), i = omd::ref_index(ref);
+    float t;
+    if (type == omd::PT_SPHERE) {
+        const uint32_t u = S.off_hot[omd::PT_SPHERE] + omd::U_XF * i;
+        if (sphere_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), r, t_min, best.t, t)) accept(best, t, ref);
+    } else if (type == omd::PT_CUBE) {
+        const uint32_t u = S.off_hot[omd::PT_CUBE] + omd::U_XF * i;
+        int axis;
+        if (cube_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), r, t_min, best.t, t, axis)) accept(best, t, ref);
+    } else if (type == omd::PT_PLANE) {
+        const uint32_t u = S.off_hot[omd::PT_PLANE] + omd::U_PLANE * i;
+        if (plane_t(sv.hot(u), sv.hot(u + 1), r, t_min, best.t, t)) accept(best, t, ref);
+    } else {
+        const uint32_t u = S.off_hot[type] + omd::U_BARY * i;
+        if (bary_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), sv.hot(u + 3), type == omd::PT_TRI, r, t_min, best.t, t)) accept(best, t, ref);
+    }
+}
+
+struct Counters {
+    uint32_t segments, node_visits, prim_tests, sdf_evals, march_steps, normal_evals, march_entered;
+};
+
+// slab test of one box against the ray; returns entry distance, or +INF when missed
+__device__ __forceinline__ float slab(float lx, float ly, float lz, float hx, float hy, float hz, V3 inv, V3 oinv, float t_min, float t_max) {
+    const float ax = lx * inv.x - oinv.x, bx = hx * inv.x - oinv.x;
+    const float ay = ly * inv.y - oinv.y, by = hy * inv.y - oinv.y;
+    const float az = lz * inv.z - oinv.z, bz = hz * inv.z - oinv.z;
+    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_max));
+    return tn <= tf ? tn : kInf;
+}
+
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ void traverse_bvh(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, Best& best, Counters& cn) {
+    if (S.n_nodes == 0) return;
+    const V3 inv = v3(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
+    const V3 oinv = v3(r.o.x * inv.x, r.o.y * inv.y, r.o.z * inv.z);
+    int2 stack[64];
+    int sp = 0;
+    int cur = 0;
+    for (;;) {
+        // cur >= 0: inner node
+        const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
+        const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
+        if (COUNT) cn.node_visits++;
+        const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, inv, oinv, t_min, best.t);
+        const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, inv, oinv, t_min, best.t);
+        int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
+        bool have;
+        if (tl < kInf && tr < kInf) {
+            int nearc = cl, farc = cr;
+            float tfar = tr;
+            if (tr < tl) { nearc = cr; farc = cl; tfar = tl; }
+            if (sp < 64) { stack[sp] = make_int2(farc, __float_as_int(tfar)); sp++; }
+            cur = nearc;
+            have = true;
+        } else if (tl < kInf) { cur = cl; have = true; }
+        else if (tr < kInf) { cur = cr; have = true; }
+        else have = false;
+        for (;;) {
+            if (have) {
+                if (cur >= 0) break;  // inner node: continue the outer loop
+                if (COUNT) cn.prim_tests++;
+                test_prim(sv, S, (uint32_t)(~cur), r, t_min, best);
+            }
+            // pop
+            have = false;
+            while (sp > 0) {
+                sp--;
+                const int2 e = stack[sp];
+                if (__int_as_float(e.y) <= best.t) { cur = e.x; have = true; break; }
+            }
+            if (!have) return;
+        }
+    }
+}
+
+// FrozenHittableList::hit, traced part (hits.rs:270-286)
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ Best closest_traced(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, Counters& cn) {
+    Best best;
+    best.t = t_max;
+    best.ref = omd::REF_NONE;
+    if (brute) {
+        for (uint32_t type = 0; type < 5; type++)
+            for (uint32_t i = 0; i < S.n[type]; i++) {
+                if (COUNT) cn.prim_tests++;
+                test_prim(sv, S, omd::make_ref(type, i), r, t_min, best);
+            }
+        return best;
+    }
+    for (uint32_t k = 0; k < S.n_large; k++) {
+        const float4 q = sv.hot(S.off_large + (k >> 2));
+        const uint32_t sel = k & 3u;
+        const uint32_t ref = __float_as_uint(sel == 0 ? q.x : (sel == 1 ? q.y : (sel == 2 ? q.z : q.w)));
+        if (COUNT) cn.prim_tests++;
+        test_prim(sv, S, ref, r, t_min, best);
+    }
+    traverse_bvh<SMEM, COUNT>(sv, S, r, t_min, best, cn);
+    return best;
+}
+
+// ---- marched objects (marched.rs) --------------------------------------------------------------
+// |Marched::sdf| of object `ref` at world point p (marched.rs:14-18)
+__device__ __forceinline__ float torus_local_sdf(V3 p, float R, float rr) {  // marched.rs:134-138
+    const float qx = sqrtf(p.x * p.x + p.z * p.z) - R;
+    return sqrtf(qx * qx + p.y * p.y) - rr;
+}
+__device__ __forceinline__ float box_local_sdf(V3 p, V3 sizes) {  // marched.rs:86-89
+    const V3 q = om::vabs(p) - sizes;
+    const V3 qm = v3(fmaxf(q.x, 0.f), fmaxf(q.y, 0.f), fmaxf(q.z, 0.f));
+    return om::length(qm) + fminf(fmaxf(q.x, fmaxf(q.y, q.z)), 0.f);
+}
+template <bool SMEM>
+__device__ __forceinline__ V3 torus_to_local(const SceneView<SMEM>& sv, uint32_t u, V3 p) {  // marched.rs:142-144
+    const float4 r0 = sv.hot(u), r1 = sv.hot(u + 1), r2 = sv.hot(u + 2), si = sv.hot(u + 6);
+    const float qx = p.x * si.x, qy = p.y * si.y, qz = p.z * si.z, qw = 1.f * si.w;
+    return v3(r0.x * qx + r0.y * qy + r0.z * qz + r0.w * qw, r1.x * qx + r1.y * qy + r1.z * qz + r1.w * qw, r2.x * qx + r2.y * qy + r2.z * qz + r2.w * qw);
+}
+template <bool SMEM>
+__device__ __forceinline__ float marched_sdf(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t type, uint32_t i, V3 p) {
+    if (type == omd::PT_MSPHERE) {
+        const float4 cr = sv.hot(S.off_hot[omd::PT_MSPHERE] + omd::U_MSPHERE * i);
+        return om::length(p - v3(cr.x, cr.y, cr.z)) - cr.w;
+    } else if (type == omd::PT_MBOX) {
+        const uint32_t u = S.off_hot[omd::PT_MBOX] + omd::U_MBOX * i;
+        const float4 c = sv.hot(u), s = sv.hot(u + 1);
+        return box_local_sdf(p - v3(c.x, c.y, c.z), v3(s.x, s.y, s.z));
+    } else {
+        const uint32_t u = S.off_hot[omd::PT_MTORUS] + omd::U_MTORUS * i;
+        const float4 sz = sv.hot(u + 8);
+        return torus_local_sdf(torus_to_local(sv, u, p), sz.x, sz.y) * sz.z;  // to_world_f marched.rs:148-150
+    }
+}
+
+// Marched::get_outward_local_normal (marched.rs:25-44); LSDF is the object's local sdf
+template <class LSDF>
+__device__ __forceinline__ V3 numeric_local_normal(V3 p, LSDF lsdf) {
+    const float eps = 0.0000001f;
+    const float x = lsdf(v3(p.x + eps, p.y, p.z)) - lsdf(v3(p.x - eps, p.y, p.z));
+    const float y = lsdf(v3(p.x, p.y + eps, p.z)) - lsdf(v3(p.x, p.y - eps, p.z));
+    const float z = lsdf(v3(p.x, p.y, p.z + eps)) - lsdf(v3(p.x, p.y, p.z - eps));
+    const V3 normal = om::unit(v3(x, y, z));
+    const V3 dir = om::unit(normal);                         // Ray::new normalises again (ray.rs:11-13)
+    const V3 start = v3(0.f, 0.f, 0.f) + 0.f * dir;          // test_ray.at(0.)
+    const float start_val = lsdf(start);
+    const V3 end = v3(0.f, 0.f, 0.f) + 1.f * dir;            // test_ray.at(1.)
+    const float end_val = lsdf(end);
+    const float sign = (end_val > start_val) ? 1.f : -1.f;
+    return normal * sign;
+}
+// Marched::get_outward_normal (marched.rs:19-24; MarchedSphere override :60-63)
+template <bool SMEM>
+__device__ __forceinline__ V3 marched_normal(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t type, uint32_t i, V3 p) {
+    if (type == omd::PT_MSPHERE) {
+        const float4 cr = sv.hot(S.off_hot[omd::PT_MSPHERE] + omd::U_MSPHERE * i);
+        return om::unit(p - v3(cr.x, cr.y, cr.z));
+    } else if (type == omd::PT_MBOX) {
+        const uint32_t u = S.off_hot[omd::PT_MBOX] + omd::U_MBOX * i;
+        const float4 c = sv.hot(u), s = sv.hot(u + 1);
+        const V3 sizes = v3(s.x, s.y, s.z);
+        const V3 n = numeric_local_normal(p - v3(c.x, c.y, c.z), [&](V3 q) { return box_local_sdf(q, sizes); });
+        // to_world of a vector: n + n.w * center with n.w = 0 (marched.rs:96-98)
+        return om::unit(v3(n.x + 0.f * c.x, n.y + 0.f * c.y, n.z + 0.f * c.z));
+    } else {
+        const uint32_t u = S.off_hot[omd::PT_MTORUS] + omd::U_MTORUS * i;
+        const float4 sz = sv.hot(u + 8);
+        const V3 n = numeric_local_normal(torus_to_local(sv, u, p), [&](V3 q) { return torus_local_sdf(q, sz.x, sz.y); });
+        const float4 r0 = sv.hot(u + 3), r1 = sv.hot(u + 4), r2 = sv.hot(u + 5), sc = sv.hot(u + 7);
+        const V3 w = xf_vec(r0, r1, r2, n);  // L2W_TR . (n, 0)
+        return om::unit(v3(w.x * sc.x, w.y * sc.y, w.z * sc.z));
+    }
+}
+
+struct Hit {
+    float t;
+    uint32_t ref;  // REF_NONE = miss
+    V3 point, normal;  // filled for marched hits only
+};
+
+// FrozenHittableList::hit, marched part (hits.rs:288-332) + unstuck (hits.rs:336-365)
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ void march(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, Hit& hit, Counters& cn) {
+    // A ray whose [t_min, min(t_max, closest)] span misses the padded union of the marched
+    // bounds can neither start within HIT_SIZE of a marched surface nor reach one: the
+    // reference's loop would end without touching `rec`.  Skipping it is result-identical.
+    {
+        const V3 inv = v3(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
+        const V3 oinv = v3(r.o.x * inv.x, r.o.y * inv.y, r.o.z * inv.z);
+        const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], inv, oinv, t_min, fminf(t_max, hit.t));
+        if (!(te < kInf)) {
+            // NaN rays reach here too (every comparison fails): the reference's unstuck() then
+            // finds no object (NaN < d is false) and returns the traced record unchanged.
+            return;
+        }
+    }
+    if (COUNT) cn.march_entered++;
+    const uint32_t n_ms = S.n[omd::PT_MSPHERE], n_mb = S.n[omd::PT_MBOX], n_mt = S.n[omd::PT_MTORUS];
+    // ---- unstuck ----
+    float t;
+    {
+        const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
+        float new_t = t_min;
+        float d = kInf;
+        const V3 p = ray_at(r, t_min);
+        uint32_t mtype = 0xFFFFFFFFu, mi = 0;
+        for (uint32_t i = 0; i < n_ms; i++) { const float nd = fabsf(marched_sdf(sv, S, omd::PT_MSPHERE, i, p)); if (nd < d) { d = nd; mtype = omd::PT_MSPHERE; mi = i; } }
+        for (uint32_t i = 0; i < n_mb; i++) { const float nd = fabsf(marched_sdf(sv, S, omd::PT_MBOX, i, p)); if (nd < d) { d = nd; mtype = omd::PT_MBOX; mi = i; } }
+        for (uint32_t i = 0; i < n_mt; i++) { const float nd = fabsf(marched_sdf(sv, S, omd::PT_MTORUS, i, p)); if (nd < d) { d = nd; mtype = omd::PT_MTORUS; mi = i; } }
+        if (COUNT) cn.sdf_evals += n_ms + n_mb + n_mt;
+        if (mtype == 0xFFFFFFFFu) return;  // `marched.is_none()` -> INF -> return rec
+        float aux = d;
+        int steps = 0;
+        while (aux < HIT_SIZE && steps < UNSTUCK_MAX_STEPS) {
+            new_t += MIN_STEP_SIZE;
+            aux = fabsf(marched_sdf(sv, S, mtype, mi, ray_at(r, new_t)));
+            steps++;
+            if (COUNT) cn.sdf_evals++;
+        }
+        t = new_t;
+    }
+    // ---- sphere tracing ----
+    int max_march_iter = 1024;
+    while (t < t_max && t < hit.t && max_march_iter > 0) {
+        max_march_iter--;
+        const V3 point = ray_at(r, t);
+        float distance = kInf;
+        uint32_t mtype = 0xFFFFFFFFu, mi = 0;
+        for (uint32_t i = 0; i < n_ms; i++) { const float d = fabsf(marched_sdf(sv, S, omd::PT_MSPHERE, i, point)); if (d < distance) { distance = d; mtype = omd::PT_MSPHERE; mi = i; } }
+        for (uint32_t i = 0; i < n_mb; i++) { const float d = fabsf(marched_sdf(sv, S, omd::PT_MBOX, i, point)); if (d < distance) { distance = d; mtype = omd::PT_MBOX; mi = i; } }
+        for (uint32_t i = 0; i < n_mt; i++) { const float d = fabsf(marched_sdf(sv, S, omd::PT_MTORUS, i, point)); if (d < distance) { distance = d; mtype = omd::PT_MTORUS; mi = i; } }
+        if (COUNT) { cn.march_steps++; cn.sdf_evals += n_ms + n_mb + n_mt; }
+        if (mtype == 0xFFFFFFFFu) return;  // `material.is_none()`
+        if (distance < HIT_SIZE) {
+            // The reference evaluates the normal of the nearest object at every step
+            // (hits.rs:306); only the value at the accepted point survives, so it is computed here.
+            hit.t = t;
+            hit.ref = omd::make_ref(mtype, mi);
+            hit.point = point;
+            hit.normal = marched_normal(sv, S, mtype, mi, point);
+            if (COUNT) cn.normal_evals++;
+            return;
+        }
+        t += distance;
+    }
+}
+
+// FrozenHittableList::hit (hits.rs:270-334); also first_hit (the BVH subsumes CameraHash)
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ Hit closest_hit(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, Counters& cn) {
+    if (COUNT) cn.segments++;
+    const Best b = closest_traced<SMEM, COUNT>(sv, S, r, t_min, t_max, brute, cn);
+    Hit h;
+    h.t = b.t;
+    h.ref = b.ref;
+    h.point = v3(0.f, 0.f, 0.f);
+    h.normal = v3(0.f, 0.f, 0.f);
+    if (S.n_marched) march<SMEM, COUNT>(sv, S, r, t_min, t_max, h, cn);
+    return h;
+}
+
+// ---- hit record of the winner (point, normal) and material ------------------------------------
+struct Material {
+    V3 albedo;
+    float fuzz, ior;
+    uint32_t mat_type;
+    uint32_t bloom_lo, bloom_hi;
+};
+template <bool SMEM>
+__device__ __forceinline__ Material load_material(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t ref) {
+    const uint32_t u = S.off_mat + omd::U_MAT * (S.mat_base[omd::ref_type(ref)] + omd::ref_index(ref));
+    const float4 m0 = sv.cold(u), m1 = sv.cold(u + 1);
+    Material m;
+    m.albedo = v3(m0.x, m0.y, m0.z); m.fuzz = m0.w; m.ior = m1.x; m.mat_type = __float_as_uint(m1.y);
+    m.bloom_lo = __float_as_uint(m1.z); m.bloom_hi = __float_as_uint(m1.w);
+    return m;
+}
+template <bool SMEM>
+__device__ __forceinline__ void finish_hit(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, Hit& h) {
+    const uint32_t type = omd::ref_type(h.ref), i = omd::ref_index(h.ref);
+    if (type == omd::PT_SPHERE) {  // traced.rs:57-61
+        const uint32_t u = S.off_hot[omd::PT_SPHERE] + omd::U_XF * i;
+        const float4 r0 = sv.hot(u), r1 = sv.hot(u + 1), r2 = sv.hot(u + 2);
+        Ray lr; lr.o = xf_point(r0, r1, r2, r.o); lr.d = xf_vec(r0, r1, r2, r.d);
+        const V3 local_point = ray_at(lr, h.t);
+        const uint32_t c = S.off_sph_l2w + omd::U_XF * i;
+        const float4 m0 = sv.cold(c), m1 = sv.cold(c + 1), m2 = sv.cold(c + 2);
+        h.point = xf_point(m0, m1, m2, local_point);
+        h.normal = om::unit(xf_vec(m0, m1, m2, local_point));
+    } else if (type == omd::PT_CUBE) {  // traced.rs:290-297
+        const uint32_t u = S.off_hot[omd::PT_CUBE] + omd::U_XF * i;
+        const float4 r0 = sv.hot(u), r1 = sv.hot(u + 1), r2 = sv.hot(u + 2);
+        Ray lr; lr.o = xf_point(r0, r1, r2, r.o); lr.d = xf_vec(r0, r1, r2, r.d);
+        float t; int axis = 0;
+        cube_t(r0, r1, r2, r, t_min, h.t, t, axis);  // recover the face axis of the accepted root
+        const V3 local_point = ray_at(lr, h.t);
+        const float s = copysignf(1.f, om::comp(local_point, axis));
+        const V3 ln = v3(axis == 0 ? 1.f : 0.f, axis == 1 ? 1.f : 0.f, axis == 2 ? 1.f : 0.f) * s;
+        const uint32_t c = S.off_cube_l2w + omd::U_XF * i;
+        const float4 m0 = sv.cold(c), m1 = sv.cold(c + 1), m2 = sv.cold(c + 2);
+        h.point = xf_point(m0, m1, m2, local_point);
+        h.normal = xf_vec(m0, m1, m2, ln);  // not normalised (reference quirk)
+    } else if (type == omd::PT_PLANE) {  // traced.rs:111-113
+        const uint32_t u = S.off_hot[omd::PT_PLANE] + omd::U_PLANE * i;
+        const float4 pn = sv.hot(u);
+        const V3 n = v3(pn.x, pn.y, pn.z);
+        const float div = om::dot(n, r.d);
+        h.point = ray_at(r, h.t);
+        h.normal = n * copysignf(1.f, -div);
+    } else if (type == omd::PT_TRI || type == omd::PT_PARA) {  // traced.rs:198-199
+        const uint32_t u = S.off_hot[type] + omd::U_BARY * i;
+        const float4 b = sv.hot(u + 1);
+        const V3 n = v3(b.x, b.y, b.z);
+        const float div = om::dot(n, r.d);
+        h.point = ray_at(r, h.t);
+        h.normal = n * copysignf(1.f, -div);
+    }
+    // marched hits: point/normal were set by march()
+}
+
+// ---- materials.rs --------------------------------------------------------------------------------
+__device__ __forceinline__ V3 reflect(V3 v, V3 n) { return v - 2.f * om::dot(v, n) * n; }  // :98-100
+__device__ __forceinline__ V3 refract(V3 uv, V3 n, float etai_over_etat) {                 // :102-108
+    const float cos_theta = fminf(om::dot(-uv, n), 1.0f);
+    const V3 r_out_perp = etai_over_etat * (uv + cos_theta * n);
+    const float aux = -sqrtf(fabsf(1.0f - om::length_squared(r_out_perp)));
+    return r_out_perp + aux * n;
+}
+__device__ __forceinline__ float reflectance(float cosv, float ref_idx) {  // :110-116
+    const float r0 = (1.f - ref_idx) / (1.f + ref_idx);
+    const float r0_2 = r0 * r0;
+    const float cos_5 = (1.f - cosv) * (1.f - cosv) * (1.f - cosv) * (1.f - cosv) * (1.f - cosv);
+    return r0_2 + (1.f - r0_2) * cos_5;
+}
+// Material::scatter (:39-95).  Returns the attenuation; `r` becomes the scattered ray.
+__device__ __forceinline__ V3 scatter(const Material& m, Ray& r, V3 point, V3 normal, Rng& g) {
+    V3 new_dir, att;
+    if (m.mat_type == OM_MAT_LAMBERTIAN) {
+        new_dir = normal + om::unit(rand_in_unit_sphere(g));
+        const float eps = 1e-8f;
+        if (fabsf(new_dir.x) < eps && fabsf(new_dir.y) < eps && fabsf(new_dir.z) < eps) new_dir = normal;
+        att = m.albedo;
+    } else if (m.mat_type == OM_MAT_METAL) {
+        const V3 reflected = reflect(r.d, normal);
+        const V3 s = rand_in_unit_sphere(g);  // drawn even when fuzz == 0
+        new_dir = reflected + m.fuzz * s;
+        att = m.albedo;
+    } else {
+        const V3 dir_unit = r.d;
+        const bool front_face = om::dot(dir_unit, normal) < 0.f;
+        const float refraction_ratio = front_face ? 1.0f / m.ior : m.ior;
+        const V3 n = front_face ? normal : -normal;
+        const float cos_theta = fminf(om::dot(-dir_unit, n), 1.0f);
+        const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+        const bool cannot_refract = (refraction_ratio * sin_theta) > 1.0f;
+        const bool reflect_by_reflectance = reflectance(cos_theta, refraction_ratio) > rng_f32(g);
+        new_dir = (cannot_refract || reflect_by_reflectance) ? reflect(dir_unit, n) : refract(dir_unit, n, refraction_ratio);
+        att = v3(1.f, 1.f, 1.f);
+    }
+    r.o = point;
+    r.d = om::unit(new_dir);  // Ray::new, ray.rs:11-13
+    return att;
+}
+
+// ---- camera.rs:60-74, render_thread.rs:183-192 -------------------------------------------------------
+__device__ __forceinline__ Ray camera_ray(const om_camera& c, float u, float v, V3 disc) {
+    const V3 rand_in_lens = c.lens_radius * disc;
+    const V3 up = v3(c.u_of_plane[0], c.u_of_plane[1], c.u_of_plane[2]), vp = v3(c.v_of_plane[0], c.v_of_plane[1], c.v_of_plane[2]);
+    const V3 offset = up * rand_in_lens.x + vp * rand_in_lens.y;
+    // uv_to_dir().dot((u,v,0,1)): rows (horizontal_i, vertical_i, 0, (llc-origin)_i)
+    const V3 origin = v3(c.origin[0], c.origin[1], c.origin[2]);
+    const V3 llc_o = v3(c.lower_left_corner[0], c.lower_left_corner[1], c.lower_left_corner[2]) - origin;
+    V3 direction;
+    if (kExact)
+        direction = v3(c.horizontal[0] * u + c.vertical[0] * v + 0.f * 0.f + llc_o.x, c.horizontal[1] * u + c.vertical[1] * v + 0.f * 0.f + llc_o.y,
+                       c.horizontal[2] * u + c.vertical[2] * v + 0.f * 0.f + llc_o.z);
+    else
+        direction = v3(c.horizontal[0] * u + c.vertical[0] * v + llc_o.x, c.horizontal[1] * u + c.vertical[1] * v + llc_o.y, c.horizontal[2] * u + c.vertical[2] * v + llc_o.z);
+    Ray r;
+    r.o = origin + offset;
+    r.d = om::unit(om::unit(direction - offset));  // .unit() in get_ray, again in Ray::new
+    return r;
+}
+__device__ __forceinline__ Ray primary_ray(const RenderArgs& A, uint32_t pxl, uint32_t sample, Rng& g) {
+    const uint32_t line = pxl / A.width, col = pxl - A.width * line;
+    const uint32_t code = A.jitter[sample];
+    const float i_rand = (rng_f32(g) + (float)((code >> 1) & 1u)) / 2.f;
+    const float j_rand = (rng_f32(g) + (float)(code & 1u)) / 2.f;
+    const float u = ((float)col + i_rand) / ((float)A.width - 1.f);
+    const float v = 1.0f - ((float)line + j_rand) / ((float)A.height - 1.f);
+    const V3 disc = rand_in_unit_disc(g);
+    return camera_ray(A.cam, u, v, disc);
+}
+__device__ __forceinline__ Ray center_ray(const RenderArgs& A, uint32_t pxl) {
+    const uint32_t line = pxl / A.width, col = pxl - A.width * line;
+    const float u = ((float)col + 0.5f) / ((float)A.width - 1.f);
+    const float v = 1.0f - ((float)line + 0.5f) / ((float)A.height - 1.f);
+    return camera_ray(A.cam, u, v, v3(0.f, 0.f, 0.f));
+}
+
+// ---- Stats (render_thread.rs:9-40), tone map (utils.rs:12-17, vec3.rs:73-76) ---------------------------------
+__device__ __forceinline__ uint32_t f32_as_u8(float f) {  // Rust `as u8`: saturating, NaN -> 0
+    if (!(f == f) || f <= 0.f) return 0u;
+    if (f >= 255.f) return 255u;
+    return (uint32_t)f;
+}
+__device__ __forceinline__ float tone1(float c) { return fminf(fmaxf(sqrtf(c), 0.f), 0.999f) * 256.0f; }
+__device__ __forceinline__ uint32_t tone_map_u8x3(V3 avg) {
+    return f32_as_u8(tone1(avg.x)) | (f32_as_u8(tone1(avg.y)) << 8) | (f32_as_u8(tone1(avg.z)) << 16);
+}
+struct Stats {
+    V3 sum;
+    uint32_t n;
+    float avg_depth;
+    uint32_t bad_avgs;
+    uint32_t bloom_lo, bloom_hi;
+    uint32_t color;  // packed r | g<<8 | b<<16
+};
+__device__ __forceinline__ bool stats_add(Stats& s, V3 x, float depth, uint32_t bloom_lo, uint32_t bloom_hi) {
+    const uint32_t old_color = s.color;
+    s.sum = s.sum + x;
+    s.n += 1;
+    s.color = tone_map_u8x3(om::div(s.sum, (float)s.n));
+    const uint32_t bad_run = (old_color == s.color) ? 1u : 0u;
+    s.bad_avgs += bad_run;
+    s.bad_avgs *= bad_run;
+    s.avg_depth = (((float)s.n - 1.f) * s.avg_depth + depth) / (float)s.n;
+    s.bloom_lo |= bloom_lo;
+    s.bloom_hi |= bloom_hi;
+    return s.bad_avgs >= 5u;
+}
+__device__ __forceinline__ uint32_t stats_color_of(V3 sum, uint32_t n) {
+    return n == 0u ? 0u : tone_map_u8x3(om::div(sum, (float)n));  // Stats::new: (0,0,0)
+}
+
+// ---- work -> pixel maps ---------------------------------------------------------------------------
+// Without a partition the image is walked in 8x4 tiles (one warp = one tile: coherent primary
+// rays).  With the interleaved-chunk partition (main.rs:172-189) slot k is the k-th pixel of the
+// handle's own 2730-pixel chunks.
+__device__ __forceinline__ uint32_t work_to_pixel(const RenderArgs& A, uint32_t k) {
+    if (A.live_list) return k < *A.live_count ? A.live_list[k] : 0xFFFFFFFFu;
+    if (A.part_world > 1u) {
+        const uint32_t c = (k / OM_CHUNK_PIXELS) * A.part_world + A.part_rank;
+        const uint32_t p = c * OM_CHUNK_PIXELS + (k % OM_CHUNK_PIXELS);
+        return p < A.npx ? p : 0xFFFFFFFFu;
+    }
+    const uint32_t tile = k >> 5, in = k & 31u;
+    const uint32_t x = (tile % A.tiles_x) * 8u + (in & 7u), y = (tile / A.tiles_x) * 4u + (in >> 3);
+    return (x < A.width && y < A.height) ? y * A.width + x : 0xFFFFFFFFu;
+}
+
+// ---- staging the hot image into shared memory: TMA 1-D bulk copy + mbarrier ------------------------
+__device__ __forceinline__ void stage_scene_smem(const float4* hot_g, uint32_t units) {
+    __shared__ __align__(8) unsigned long long bar;
+    const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(&bar);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t bytes = units * 16u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+        uint32_t done = 0;
+        while (done < bytes) {
+            const uint32_t chunk = min(bytes - done, 32768u);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(reinterpret_cast<char*>(om_smem) + done);
+            const char* src = reinterpret_cast<const char*>(hot_g) + done;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(chunk), "r"(bar_s)
+                         : "memory");
+            done += chunk;
+        }
+    }
+    // every thread waits for phase 0 of the barrier
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar_s) : "memory");
+    }
+}
+
+// ============================================================================================
+// k_render: persistent path-regeneration kernel.  One lane owns one pixel for the whole pass and
+// runs a per-lane state machine (new sample -> segment -> shade -> ... -> Stats::add), so lanes
+// never wait for each other's paths; the accumulators live in registers between the single
+// coalesced read and write of the pixel's 32-byte state.
+// ============================================================================================
+template <bool SMEM, bool COUNT>
+__global__ void __launch_bounds__(CTA_THREADS, 2) k_render(const __grid_constant__ RenderArgs A) {
+    if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
+    SceneView<SMEM> sv;
+    sv.hot_g = A.hot_g;
+    sv.cold_g = A.cold_g;
+    const SceneHeader& S = A.scene;
+    const bool brute = (A.flags & OM_RENDER_BRUTE_FORCE) != 0;
+    const bool adaptive = (A.flags & OM_RENDER_ADAPTIVE) != 0;
+    Counters cn = {0, 0, 0, 0, 0, 0, 0};
+    unsigned long long credited = 0, traced = 0;
+    const uint32_t lane = threadIdx.x & 31u;
+
+    for (;;) {
+        // one ticket = one warp-sized run of 32 work slots (an 8x4 pixel tile)
+        uint32_t ticket = 0;
+        if (lane == 0u) ticket = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], 1ull);
+        ticket = __shfl_sync(0xffffffffu, ticket, 0);
+        const uint32_t base = ticket * 32u;
+        if (base >= A.n_work) break;
+        const uint32_t k = base + lane;
+        const uint32_t pxl = k < A.n_work ? work_to_pixel(A, k) : 0xFFFFFFFFu;
+        if (pxl == 0xFFFFFFFFu) continue;
+
+        // ---- load Stats ----
+        Stats st;
+        {
+            const float4 a = A.acc[pxl];
+            const uint4 x = A.aux[pxl];
+            st.sum = v3(a.x, a.y, a.z); st.n = __float_as_uint(a.w);
+            st.avg_depth = __uint_as_float(x.x); st.bad_avgs = x.y; st.bloom_lo = x.z; st.bloom_hi = x.w;
+            st.color = stats_color_of(st.sum, st.n);
+        }
+        uint32_t todo = A.spp_budget > st.n ? min(A.spp_budget - st.n, A.spp_pass) : 0u;
+        if (adaptive && st.bad_avgs >= 5u) todo = 0u;
+
+        // ---- per-lane path state machine ----
+        Rng g;
+        Ray ray;
+        V3 color = v3(1.f, 1.f, 1.f);
+        uint32_t seg = 0;
+        float first_t = kInf;
+        uint32_t first_lo = 0, first_hi = 0;
+        const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;  // segment 0 + `for _i in 1..depth`
+        bool fresh = true;
+        while (todo > 0u) {
+            if (fresh) {
+                const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
+                rng_init(g, A.seed_lo, A.seed_hi, pxl, sample);
+                ray = primary_ray(A, pxl, sample, g);
+                color = v3(1.f, 1.f, 1.f);
+                seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
+                fresh = false;
+            }
+            Hit h = closest_hit<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, cn);
+            bool finished;
+            V3 result = color;
+            if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
+                finish_hit(sv, S, ray, A.tmin, h);
+                const Material m = load_material(sv, S, h.ref);
+                if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
+                color = color * scatter(m, ray, h.point, h.normal, g);
+                seg++;
+                finished = seg >= nseg;
+                if (finished) result = -v3(0.f, 0.f, 0.f);  // out of depth: -black (:142)
+            } else {  // None: sky (:117-123)
+                const float t = 0.5f * (ray.d.y + 1.0f);
+                const V3 sky = (1.0f - t) * v3(1.f, 1.f, 1.f) + t * v3(0.5f, 0.7f, 1.0f);
+                result = color * sky;
+                finished = true;
+            }
+            if (finished) {
+                bool done = stats_add(st, result, first_t, first_lo, first_hi);
+                if (!adaptive) done = false;
+                traced++;
+                todo--;
+                const uint32_t left = A.spp_budget - st.n;
+                credited += (done ? (unsigned long long)left : 0ull) + 1ull;  // render_thread.rs:196-198
+                if (done) todo = 0u;
+                fresh = true;
+            }
+        }
+        // ---- store Stats ----
+        A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
+        A.aux[pxl] = make_uint4(__float_as_uint(st.avg_depth), st.bad_avgs, st.bloom_lo, st.bloom_hi);
+    }
+
+    // ---- progress counters: warp-aggregate, one atomic per warp ----
+    for (int o = 16; o > 0; o >>= 1) {
+        credited += __shfl_xor_sync(0xffffffffu, credited, o);
+        traced += __shfl_xor_sync(0xffffffffu, traced, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (credited) atomicAdd(&A.counters[CTR_CREDITED], credited);
+        if (traced) atomicAdd(&A.counters[CTR_TRACED], traced);
+    }
+    if (COUNT) {
+        unsigned long long v[7] = {cn.segments, cn.node_visits, cn.prim_tests, cn.sdf_evals, cn.march_steps, cn.normal_evals, cn.march_entered};
+        for (int i = 0; i < 7; i++) {
+            for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+            if ((threadIdx.x & 31) == 0 && v[i]) atomicAdd(&A.counters[CTR_SEGMENTS + i], v[i]);
+        }
+    }
+}
+
+// ============================================================================================
+// parity hooks
+// ============================================================================================
+// primary-ray closest hit per pixel: (obj_id, t) — what ray_color reports as (obj_id, depthf)
+template <bool SMEM>
+__global__ void __launch_bounds__(CTA_THREADS, 2) k_primary(const __grid_constant__ RenderArgs A, uint32_t mode, uint32_t sample_index, unsigned long long* ids, float* tout) {
+    if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
+    SceneView<SMEM> sv;
+    sv.hot_g = A.hot_g;
+    sv.cold_g = A.cold_g;
+    Counters cn = {0, 0, 0, 0, 0, 0, 0};
+    for (uint32_t pxl = blockIdx.x * CTA_THREADS + threadIdx.x; pxl < A.npx; pxl += gridDim.x * CTA_THREADS) {
+        Ray ray;
+        if (mode == 0u) ray = center_ray(A, pxl);
+        else { Rng g; rng_init(g, A.seed_lo, A.seed_hi, pxl, sample_index); ray = primary_ray(A, pxl, sample_index, g); }
+        const Hit h = closest_hit<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, cn);
+        if (h.ref == omd::REF_NONE) { ids[pxl] = 0ull; tout[pxl] = kInf; }
+        else { ids[pxl] = ((unsigned long long)(omd::ref_type(h.ref) + 1u) << 32) | (unsigned long long)(omd::ref_index(h.ref) + 1u); tout[pxl] = h.t; }
+    }
+}
+
+// FrozenHittableList::hit for arbitrary rays (dirs normalised like Ray::new)
+template <bool SMEM>
+__global__ void __launch_bounds__(CTA_THREADS, 2) k_trace_rays(const __grid_constant__ TraceArgs A) {
+    if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
+    SceneView<SMEM> sv;
+    sv.hot_g = A.hot_g;
+    sv.cold_g = A.cold_g;
+    Counters cn = {0, 0, 0, 0, 0, 0, 0};
+    for (uint32_t i = blockIdx.x * CTA_THREADS + threadIdx.x; i < A.n; i += gridDim.x * CTA_THREADS) {
+        Ray ray;
+        ray.o = v3(A.origins[3 * i], A.origins[3 * i + 1], A.origins[3 * i + 2]);
+        ray.d = om::unit(v3(A.dirs[3 * i], A.dirs[3 * i + 1], A.dirs[3 * i + 2]));
+        Hit h = closest_hit<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, cn);
+        const bool hit = h.ref != omd::REF_NONE;
+        if (hit) finish_hit(sv, A.scene, ray, A.tmin, h);
+        if (A.ids) A.ids[i] = hit ? (((unsigned long long)(omd::ref_type(h.ref) + 1u) << 32) | (unsigned long long)(omd::ref_index(h.ref) + 1u)) : 0ull;
+        if (A.t) A.t[i] = hit ? h.t : kInf;
+        if (A.points) { A.points[3 * i] = hit ? h.point.x : 0.f; A.points[3 * i + 1] = hit ? h.point.y : 0.f; A.points[3 * i + 2] = hit ? h.point.z : 0.f; }
+        if (A.normals) { A.normals[3 * i] = hit ? h.normal.x : 0.f; A.normals[3 * i + 1] = hit ? h.normal.y : 0.f; A.normals[3 * i + 2] = hit ? h.normal.z : 0.f; }
+    }
+}
+
+}  // namespace OM_NS

@@ -1,0 +1,47 @@
+// Host-side launch wrappers, compiled once per build of om_device.cuh (namespace OM_NS).
+namespace OM_NS {
+
+template <class K>
+static cudaError_t prep(K kern, size_t smem_bytes) {
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+}
+
+// resident CTAs per SM of the render kernel for this configuration
+int render_occupancy(bool smem, bool count, size_t smem_bytes) {
+    int n = 0;
+    cudaError_t e;
+    if (smem) {
+        if (count) { prep(k_render<true, true>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, true>, CTA_THREADS, smem_bytes); }
+        else { prep(k_render<true, false>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, false>, CTA_THREADS, smem_bytes); }
+    } else {
+        if (count) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, true>, CTA_THREADS, 0);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, false>, CTA_THREADS, 0);
+    }
+    return e == cudaSuccess ? n : 0;
+}
+
+cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st) {
+    if (smem) {
+        if (count) { prep(k_render<true, true>, smem_bytes); k_render<true, true><<<grid, CTA_THREADS, smem_bytes, st>>>(a); }
+        else { prep(k_render<true, false>, smem_bytes); k_render<true, false><<<grid, CTA_THREADS, smem_bytes, st>>>(a); }
+    } else {
+        if (count) k_render<false, true><<<grid, CTA_THREADS, 0, st>>>(a);
+        else k_render<false, false><<<grid, CTA_THREADS, 0, st>>>(a);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_primary(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st, uint32_t mode, uint32_t sample_index,
+                           unsigned long long* ids, float* t) {
+    if (smem) { prep(k_primary<true>, smem_bytes); k_primary<true><<<grid, CTA_THREADS, smem_bytes, st>>>(a, mode, sample_index, ids, t); }
+    else k_primary<false><<<grid, CTA_THREADS, 0, st>>>(a, mode, sample_index, ids, t);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace(const omk::TraceArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st) {
+    if (smem) { prep(k_trace_rays<true>, smem_bytes); k_trace_rays<true><<<grid, CTA_THREADS, smem_bytes, st>>>(a); }
+    else k_trace_rays<false><<<grid, CTA_THREADS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace OM_NS

@@ -1,0 +1,233 @@
+#include "om_scene.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <limits>
+
+#include "om_bvh.h"
+
+namespace oms {
+namespace {
+using omb::Aabb;
+const float kInf = std::numeric_limits<float>::infinity();
+
+// Pad a box so that every ray the f32 intersection routine reports as a hit also overlaps the
+// box: rounding in the primitive tests moves a reported hit by far less than this margin.
+Aabb padded(const double lo[3], const double hi[3]) {
+    Aabb b;
+    for (int a = 0; a < 3; a++) {
+        const double ext = hi[a] - lo[a];
+        const double mag = std::max(std::fabs(lo[a]), std::fabs(hi[a]));
+        const double eps = 1e-4 * std::max(ext, mag) + 1e-5;
+        b.lo[a] = nextafterf(float(lo[a] - eps), -kInf);
+        b.hi[a] = nextafterf(float(hi[a] + eps), kInf);
+    }
+    return b;
+}
+
+// traced.rs:65-70 boxes the unit sphere's +-1 cube; the exact extent of an ellipsoid M*S^2 along
+// axis i is the norm of row i of the linear part.
+Aabb sphere_box(const om_sphere& s) {
+    const float* m = s.m_local_to_world;
+    double lo[3], hi[3];
+    for (int i = 0; i < 3; i++) {
+        const double h = std::sqrt(double(m[4 * i]) * m[4 * i] + double(m[4 * i + 1]) * m[4 * i + 1] + double(m[4 * i + 2]) * m[4 * i + 2]);
+        lo[i] = m[4 * i + 3] - h;
+        hi[i] = m[4 * i + 3] + h;
+    }
+    return padded(lo, hi);
+}
+// traced.rs:301-304 uses +-1; the cube really spans +-0.5 (traced.rs:273-274)
+Aabb cube_box(const om_cube& s) {
+    const float* m = s.m_local_to_world;
+    double lo[3], hi[3];
+    for (int i = 0; i < 3; i++) {
+        const double h = 0.5 * (std::fabs(double(m[4 * i])) + std::fabs(double(m[4 * i + 1])) + std::fabs(double(m[4 * i + 2])));
+        lo[i] = m[4 * i + 3] - h;
+        hi[i] = m[4 * i + 3] + h;
+    }
+    return padded(lo, hi);
+}
+// traced.rs:208-219 is marked "may be wrong" in the reference; use the real vertices.
+Aabb bary_box(const om_barycentric& b, bool parallelogram) {
+    double lo[3], hi[3];
+    for (int i = 0; i < 3; i++) {
+        const double o = b.origin[i], pu = o + double(b.u[i]) * b.u_length, pv = o + double(b.v[i]) * b.v_length;
+        lo[i] = std::min(o, std::min(pu, pv));
+        hi[i] = std::max(o, std::max(pu, pv));
+        if (parallelogram) { const double puv = pu + double(b.v[i]) * b.v_length; lo[i] = std::min(lo[i], puv); hi[i] = std::max(hi[i], puv); }
+    }
+    return padded(lo, hi);
+}
+double half_area(const Aabb& b) {
+    const double dx = double(b.hi[0]) - b.lo[0], dy = double(b.hi[1]) - b.lo[1], dz = double(b.hi[2]) - b.lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+struct Packer {
+    std::vector<float>& v;
+    explicit Packer(std::vector<float>& v_) : v(v_) {}
+    uint32_t units() const { return uint32_t(v.size() / 4); }
+    void f4(float a, float b, float c, float d) { v.push_back(a); v.push_back(b); v.push_back(c); v.push_back(d); }
+    void rows3(const float* m) { for (int r = 0; r < 3; r++) f4(m[4 * r], m[4 * r + 1], m[4 * r + 2], m[4 * r + 3]); }
+    void u4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) { float f[4]; uint32_t u[4] = {a, b, c, d}; memcpy(f, u, 16); f4(f[0], f[1], f[2], f[3]); }
+};
+float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+
+void pack_material(Packer& p, const om_material& m, uint32_t pt, size_t index) {
+    const uint64_t id = OM_OBJ_ID(pt + 1, index);  // ABI type tag = scan-order code + 1
+    const uint64_t bloom = omh::bloom_get_hash(id);
+    p.f4(m.albedo[0], m.albedo[1], m.albedo[2], m.fuzz);
+    p.f4(m.ior, u2f(m.mat_type), u2f(uint32_t(bloom)), u2f(uint32_t(bloom >> 32)));
+}
+}  // namespace
+
+void freeze(const omh::SceneLists& L, uint32_t flags, FrozenScene& out) {
+    using namespace omd;
+    SceneHeader& h = out.hdr;
+    memset(&h, 0, sizeof h);
+    out.hot.clear();
+    out.cold.clear();
+    h.n[PT_SPHERE] = uint32_t(L.spheres.size());   h.n[PT_CUBE] = uint32_t(L.cubes.size());
+    h.n[PT_TRI] = uint32_t(L.triangles.size());    h.n[PT_PLANE] = uint32_t(L.infinite_planes.size());
+    h.n[PT_PARA] = uint32_t(L.parallelograms.size());
+    h.n[PT_MSPHERE] = uint32_t(L.marched_spheres.size()); h.n[PT_MBOX] = uint32_t(L.marched_boxes.size());
+    h.n[PT_MTORUS] = uint32_t(L.marched_tori.size());
+    out.n_total = 0;
+    for (int i = 0; i < 8; i++) out.n_total += h.n[i];
+
+    // ---- bounded traced primitives -> BVH; unbounded / scene-sized ones -> always-test list ----
+    std::vector<uint32_t> refs;
+    std::vector<Aabb> boxes;
+    for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i])); }
+    for (size_t i = 0; i < L.cubes.size(); i++) { refs.push_back(make_ref(PT_CUBE, uint32_t(i))); boxes.push_back(cube_box(L.cubes[i])); }
+    for (size_t i = 0; i < L.triangles.size(); i++) { refs.push_back(make_ref(PT_TRI, uint32_t(i))); boxes.push_back(bary_box(L.triangles[i], false)); }
+    for (size_t i = 0; i < L.parallelograms.size(); i++) { refs.push_back(make_ref(PT_PARA, uint32_t(i))); boxes.push_back(bary_box(L.parallelograms[i], true)); }
+    std::vector<uint32_t> large;
+    for (size_t i = 0; i < L.infinite_planes.size(); i++) large.push_back(make_ref(PT_PLANE, uint32_t(i)));  // Bounded default: +-INF (bounding_box.rs:69-73)
+    if (!(flags & 1u) && refs.size() > 4) {
+        // An object whose box is a large share of the whole scene (the r=1000 ground sphere,
+        // main.rs:41) overlaps every subtree: test it once per ray instead.
+        Aabb all;
+        for (int a = 0; a < 3; a++) { all.lo[a] = kInf; all.hi[a] = -kInf; }
+        for (const Aabb& b : boxes) for (int a = 0; a < 3; a++) { all.lo[a] = std::min(all.lo[a], b.lo[a]); all.hi[a] = std::max(all.hi[a], b.hi[a]); }
+        const double total = half_area(all);
+        std::vector<uint32_t> r2; std::vector<Aabb> b2;
+        for (size_t i = 0; i < refs.size(); i++) {
+            const bool nonfinite = !std::isfinite(half_area(boxes[i]));
+            if ((nonfinite || half_area(boxes[i]) >= 0.25 * total) && large.size() < 64) large.push_back(refs[i]);
+            else { r2.push_back(refs[i]); b2.push_back(boxes[i]); }
+        }
+        refs.swap(r2); boxes.swap(b2);
+    }
+    std::sort(large.begin(), large.end());
+    omb::BuildResult bvh;
+    omb::build(refs, boxes, bvh);
+    h.n_nodes = uint32_t(bvh.nodes.size());
+    h.n_large = uint32_t(large.size());
+    h.n_bvh_prims = uint32_t(refs.size());
+    h.bvh_depth = bvh.depth;
+
+    // ---- hot image ----------------------------------------------------------------------------
+    Packer hot(out.hot);
+    h.off_nodes = hot.units();
+    for (const omb::Node& nd : bvh.nodes) {
+        hot.f4(nd.lmin[0], nd.lmin[1], nd.lmin[2], nd.lmax[0]);
+        hot.f4(nd.lmax[1], nd.lmax[2], nd.rmin[0], nd.rmin[1]);
+        hot.f4(nd.rmin[2], nd.rmax[0], nd.rmax[1], nd.rmax[2]);
+        hot.u4(uint32_t(nd.left), uint32_t(nd.right), 0u, 0u);
+    }
+    h.off_hot[PT_SPHERE] = hot.units();
+    for (const om_sphere& s : L.spheres) hot.rows3(s.m_world_to_local);
+    h.off_hot[PT_CUBE] = hot.units();
+    for (const om_cube& s : L.cubes) hot.rows3(s.m_world_to_local);
+    auto pack_bary = [&](const om_barycentric& b) {
+        // only rows 0 and 2 of base_inv and the x/z of v_in_base are read (traced.rs:155-167)
+        hot.f4(b.origin[0], b.origin[1], b.origin[2], b.u_length);
+        hot.f4(b.uxv[0], b.uxv[1], b.uxv[2], b.v_length);
+        hot.f4(b.base_inv[0], b.base_inv[1], b.base_inv[2], b.v_in_base[0]);
+        hot.f4(b.base_inv[6], b.base_inv[7], b.base_inv[8], b.v_in_base[2]);
+    };
+    h.off_hot[PT_TRI] = hot.units();
+    for (const om_barycentric& b : L.triangles) pack_bary(b);
+    h.off_hot[PT_PLANE] = hot.units();
+    for (const om_infinite_plane& p : L.infinite_planes) { hot.f4(p.normal[0], p.normal[1], p.normal[2], 0.f); hot.f4(p.center[0], p.center[1], p.center[2], 0.f); }
+    h.off_hot[PT_PARA] = hot.units();
+    for (const om_barycentric& b : L.parallelograms) pack_bary(b);
+    h.off_large = hot.units();
+    for (size_t i = 0; i < large.size(); i += 4) {
+        uint32_t q[4] = {REF_NONE, REF_NONE, REF_NONE, REF_NONE};
+        for (size_t k = 0; k < 4 && i + k < large.size(); k++) q[k] = large[i + k];
+        hot.u4(q[0], q[1], q[2], q[3]);
+    }
+    // marched objects and their bounds
+    double mlo[3] = {1e300, 1e300, 1e300}, mhi[3] = {-1e300, -1e300, -1e300};
+    auto grow = [&](const double lo[3], const double hi[3]) { for (int a = 0; a < 3; a++) { mlo[a] = std::min(mlo[a], lo[a]); mhi[a] = std::max(mhi[a], hi[a]); } };
+    const double HIT = 0.001;  // hits.rs:113
+    h.off_hot[PT_MSPHERE] = hot.units();
+    for (const om_marched_sphere& s : L.marched_spheres) {
+        hot.f4(s.center[0], s.center[1], s.center[2], s.radius);
+        double lo[3], hi[3];
+        const double r = std::fabs(double(s.radius)) + 4 * HIT;
+        for (int a = 0; a < 3; a++) { lo[a] = s.center[a] - r * 1.001; hi[a] = s.center[a] + r * 1.001; }
+        grow(lo, hi);
+    }
+    h.off_hot[PT_MBOX] = hot.units();
+    for (const om_marched_box& s : L.marched_boxes) {
+        hot.f4(s.center[0], s.center[1], s.center[2], 0.f);
+        hot.f4(s.sizes[0], s.sizes[1], s.sizes[2], 0.f);
+        double lo[3], hi[3];
+        for (int a = 0; a < 3; a++) { const double r = (std::fabs(double(s.sizes[a])) + 4 * HIT) * 1.001; lo[a] = s.center[a] - r; hi[a] = s.center[a] + r; }
+        grow(lo, hi);
+    }
+    h.off_hot[PT_MTORUS] = hot.units();
+    for (const om_marched_torus& s : L.marched_tori) {
+        hot.rows3(s.m_world_to_local_translate_rotate);
+        hot.rows3(s.m_local_to_world_translate_rotate);
+        hot.f4(s.m_world_to_local_scale[0], s.m_world_to_local_scale[1], s.m_world_to_local_scale[2], s.m_world_to_local_scale[3]);
+        hot.f4(s.m_local_to_world_scale[0], s.m_local_to_world_scale[1], s.m_local_to_world_scale[2], s.m_local_to_world_scale[3]);
+        const float mins = fminf(s.m_local_to_world_scale[0], fminf(s.m_local_to_world_scale[1], s.m_local_to_world_scale[2]));  // marched.rs:148-150
+        hot.f4(s.sizes[0], s.sizes[1], mins, 0.f);
+        // |sdf| < HIT  <=>  local distance < HIT / min_scale; local torus inside a ball of radius R + r
+        // around the TR translation; world point = (TR q) * scale componentwise (marched.rs:142-147)
+        const double maxs = std::max(std::fabs(double(s.m_local_to_world_scale[0])), std::max(std::fabs(double(s.m_local_to_world_scale[1])), std::fabs(double(s.m_local_to_world_scale[2]))));
+        const double rad = (std::fabs(double(s.sizes[0])) + std::fabs(double(s.sizes[1])) + 4 * HIT / std::max(1e-12, double(std::fabs(mins)))) * 1.001;
+        double lo[3], hi[3];
+        for (int a = 0; a < 3; a++) {
+            const double c = s.m_local_to_world_translate_rotate[4 * a + 3], sc = s.m_local_to_world_scale[a];
+            const double p0 = (c - rad) * sc, p1 = (c + rad) * sc;
+            lo[a] = std::min(p0, p1) - 4 * HIT * maxs; hi[a] = std::max(p0, p1) + 4 * HIT * maxs;
+        }
+        grow(lo, hi);
+    }
+    h.n_marched = h.n[PT_MSPHERE] + h.n[PT_MBOX] + h.n[PT_MTORUS];
+    for (int a = 0; a < 3; a++) {
+        if (h.n_marched == 0) { h.march_lo[a] = kInf; h.march_hi[a] = -kInf; }
+        else { h.march_lo[a] = nextafterf(float(mlo[a]), -kInf); h.march_hi[a] = nextafterf(float(mhi[a]), kInf); }
+    }
+    h.hot_units = hot.units();
+
+    // ---- cold image ---------------------------------------------------------------------------
+    Packer cold(out.cold);
+    h.off_sph_l2w = cold.units();
+    for (const om_sphere& s : L.spheres) cold.rows3(s.m_local_to_world);
+    h.off_cube_l2w = cold.units();
+    for (const om_cube& s : L.cubes) cold.rows3(s.m_local_to_world);
+    h.off_mat = cold.units();
+    uint32_t base = 0;
+    auto mats = [&](uint32_t pt, auto const& list) {
+        h.mat_base[pt] = base;
+        for (size_t i = 0; i < list.size(); i++) pack_material(cold, list[i].material, pt, i);
+        base += uint32_t(list.size());
+    };
+    mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
+    mats(PT_PARA, L.parallelograms); mats(PT_MSPHERE, L.marched_spheres); mats(PT_MBOX, L.marched_boxes); mats(PT_MTORUS, L.marched_tori);
+    if (cold.units() == 0) cold.f4(0, 0, 0, 0);
+    if (hot.units() == 0) hot.f4(0, 0, 0, 0);
+    h.hot_units = hot.units();
+    h.cold_units = cold.units();
+}
+
+}  // namespace oms

@@ -1,0 +1,21 @@
+// FrozenHittableList (hits.rs:63-69) as device data: HittableList::freeze packs the eight
+// object lists, their materials and a BVH into the two images described in om_dev_types.h.
+#pragma once
+#include <vector>
+
+#include "om_dev_types.h"
+#include "om_host.h"
+
+namespace oms {
+
+struct FrozenScene {
+    omd::SceneHeader hdr;
+    std::vector<float> hot;   // hdr.hot_units * 4 floats
+    std::vector<float> cold;  // hdr.cold_units * 4 floats
+    uint64_t n_total = 0;
+};
+
+// flags: bit 0 = put every bounded primitive in the BVH even when it is scene-sized
+void freeze(const omh::SceneLists& lists, uint32_t flags, FrozenScene& out);
+
+}  // namespace oms

@@ -1,0 +1,118 @@
+"""Multi-GPU split of render_thread::render: one process per GPU, torch.distributed for plumbing.
+
+The reference splits pixels over CPU threads in 2730-pixel chunks round-robin (main.rs:172-189)
+and never exchanges anything (shared memory).  Here every rank holds the whole (tiny) scene and
+renders either
+  * an spp slice  — samples [base, base+count) of every pixel (fixed-spp renders; perfectly
+    balanced), or
+  * its interleaved chunks — the reference's own split, needed for adaptive retirement —
+and ONE exchange at the end brings the accumulators to rank 0: a SUM reduce of
+{sum.rgb, n, n*avg_depth, bad_avgs} and a gather + bitwise OR of the 64-bit bloom masks (NCCL has
+no OR).  The merge arithmetic is plain tensor code so the gloo/CPU tests exercise the same path.
+"""
+import numpy as np
+
+from . import _abi as A
+
+
+def spp_slices(spp_total: int, world: int):
+    """[(base, count)] per rank; counts differ by at most 1 and sum to spp_total."""
+    q, r = divmod(spp_total, world)
+    out, base = [], 0
+    for k in range(world):
+        c = q + (1 if k < r else 0)
+        out.append((base, c))
+        base += c
+    return out
+
+
+def owned_pixel_mask(npx: int, rank: int, world: int):
+    """Interleaved-chunk ownership, main.rs:172-189 with thread id -> rank."""
+    idx = np.arange(npx, dtype=np.int64)
+    return (idx // A.CHUNK_PIXELS) % max(world, 1) == rank
+
+
+def pixels_to_accum(px):
+    """om_pixel array -> (acc [npx,8] float32, bloom [npx] int64) in the export layout of
+    om_render_export_accum: {sum.r,sum.g,sum.b,n, n*avg_depth, bad_avgs, 0, 0}."""
+    n = px["n"].astype(np.float32)
+    acc = np.zeros((px.shape[0], 8), np.float32)
+    acc[:, 0:3] = px["sum"]
+    acc[:, 3] = n
+    with np.errstate(invalid="ignore"):
+        acc[:, 4] = np.where(n > 0, n * px["avg_depth"], 0.0)
+    acc[:, 5] = px["bad_avgs"].astype(np.float32)
+    return acc, px["bloom"].view(np.int64).copy()
+
+
+def merge_accum(acc_list, bloom_list):
+    """What the collective computes: elementwise SUM of acc, bitwise OR of bloom."""
+    acc = np.sum(np.stack(acc_list, 0), axis=0, dtype=np.float32)
+    bloom = np.bitwise_or.reduce(np.stack(bloom_list, 0), axis=0)
+    return acc, bloom
+
+
+def reduce_to_rank0(acc_t, bloom_t, group=None):
+    """acc_t: float32 tensor [npx,8]; bloom_t: int64 tensor [npx], both on this rank's device.
+    After the call rank 0 holds the merged values in place.  One reduce + one gather."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if world == 1:
+        return acc_t, bloom_t
+    dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM, group=group)
+    gathered = [torch.empty_like(bloom_t) for _ in range(world)] if rank == 0 else None
+    dist.gather(bloom_t, gather_list=gathered, dst=0, group=group)
+    if rank == 0:
+        stacked = torch.stack(gathered, 0)
+        if stacked.is_cuda:
+            from . import _lib
+            _lib.call("om_bloom_or", bloom_t.data_ptr(), stacked.data_ptr(), world, bloom_t.numel(), bloom_t.device.index)
+        else:
+            out = stacked[0].clone()
+            for k in range(1, world):
+                out |= stacked[k]
+            bloom_t.copy_(out)
+    return acc_t, bloom_t
+
+
+class DistributedRenderer:
+    """One rank's share of a render plus the final exchange.  `mode` is "spp" or "chunks"."""
+
+    def __init__(self, frozen, cam, width, height, spp, rank, world, mode="spp", device=None, **kw):
+        import torch
+        from . import api
+
+        self.torch = torch
+        self.rank, self.world, self.mode = rank, world, mode
+        self.device = torch.cuda.current_device() if device is None else device
+        flags = kw.pop("flags", 0)
+        if mode == "spp":
+            base, count = spp_slices(spp, world)[rank]
+            if count == 0:
+                raise ValueError("fewer samples than ranks")
+            p = api.render_params(width, height, spp, flags=flags, sample_base=base, sample_count=count, device=self.device, **kw)
+        else:
+            p = api.render_params(width, height, spp, flags=flags, part_rank=rank, part_world=world, device=self.device, **kw)
+        self.params = p
+        self.r = api.Renderer(frozen, cam, p)
+        npx = width * height
+        dev = torch.device("cuda", self.device)
+        self.acc = torch.empty((npx, 8), dtype=torch.float32, device=dev)
+        self.bloom = torch.empty((npx,), dtype=torch.int64, device=dev)
+
+    def render(self):
+        self.r.launch(0)
+
+    def exchange(self):
+        """export -> collective -> import on rank 0.  Returns after rank 0 holds the full image."""
+        self.r.export_accum(self.acc.data_ptr(), self.bloom.data_ptr())
+        reduce_to_rank0(self.acc, self.bloom)
+        if self.rank == 0 and self.world > 1:
+            self.torch.cuda.synchronize(self.device)
+            self.r.import_accum(self.acc.data_ptr(), self.bloom.data_ptr())
+
+    def close(self):
+        self.r.close()
