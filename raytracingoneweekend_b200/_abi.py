@@ -22,7 +22,7 @@ TYPE_SPHERE, TYPE_CUBE, TYPE_TRIANGLE, TYPE_INFINITE_PLANE, TYPE_PARALLELOGRAM =
 TYPE_MARCHED_SPHERE, TYPE_MARCHED_BOX, TYPE_MARCHED_TORUS = 6, 7, 8
 
 RENDER_ADAPTIVE = 1 << 0
-RENDER_EXACT = 1 << 1
+RENDER_FAST_MATH = 1 << 1
 RENDER_BRUTE_FORCE = 1 << 2
 RENDER_WAVEFRONT = 1 << 3
 RENDER_NO_SMEM_SCENE = 1 << 4

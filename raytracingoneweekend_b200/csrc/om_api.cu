@@ -185,10 +185,10 @@ om_status om_scene_generate(om_scene* s, uint32_t kind, uint64_t seed, uint64_t 
     if (!omh::generate(s->lists, kind, seed, n_param)) return fail(OM_ERR_INVALID, "om_scene_generate: unknown kind %u", kind);
     return OM_OK;
 }
-om_status om_scene_freeze(om_scene* s, const om_camera*, uint32_t flags) {
+om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags) {
     if (!s) return fail(OM_ERR_INVALID, "om_scene_freeze: NULL scene");
     s->release_device();
-    oms::freeze(s->lists, flags, s->fz);
+    oms::freeze(s->lists, cam, flags, s->fz);
     s->frozen = true;
     return OM_OK;
 }

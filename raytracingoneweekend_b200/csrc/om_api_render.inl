@@ -267,7 +267,7 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             CU(cudaMalloc(&r->live_count, sizeof(uint32_t)));
         }
         // launch shape: persistent grid, hot image in shared memory when two CTAs still fit per SM
-        const bool exact = (p.flags & OM_RENDER_EXACT) != 0, count = (p.flags & OM_RENDER_COUNTERS) != 0;
+        const bool exact = (p.flags & OM_RENDER_FAST_MATH) == 0, count = (p.flags & OM_RENDER_COUNTERS) != 0;
         const size_t hot_bytes = size_t(r->scene->fz.hdr.hot_units) * 16u;
         r->use_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= r->props.smem_optin / 2;
         r->smem_bytes = r->use_smem ? hot_bytes : 0;
@@ -317,7 +317,7 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     else { CU(cudaEventCreate(&ev.a)); CU(cudaEventCreate(&ev.b)); }
     CU(cudaMemsetAsync(r->counters + omk::ctr::CTR_TICKET, 0, sizeof(unsigned long long), r->stream));
     CU(cudaEventRecord(ev.a, r->stream));
-    const bool exact = (r->p.flags & OM_RENDER_EXACT) != 0, count = (r->p.flags & OM_RENDER_COUNTERS) != 0;
+    const bool exact = (r->p.flags & OM_RENDER_FAST_MATH) == 0, count = (r->p.flags & OM_RENDER_COUNTERS) != 0;
     cudaError_t e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
                           : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
     if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
@@ -406,7 +406,7 @@ om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_index, 
     float* d_t = (float*)(d_ids + n);
     omk::RenderArgs a = make_args(r);
     const int grid = std::min(ublocks(n), r->props.sms * 8);
-    cudaError_t e = (r->p.flags & OM_RENDER_EXACT) ? om_exact::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t)
+    cudaError_t e = !(r->p.flags & OM_RENDER_FAST_MATH) ? om_exact::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t)
                                                    : om_fast::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t);
     if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_primary launch failed: %s", cudaGetErrorString(e));
     CU(cudaMemcpyAsync(ids, d_ids, n * 8u, cudaMemcpyDeviceToHost, r->stream));
@@ -480,7 +480,7 @@ om_status om_trace_rays(const om_scene* frozen, const float* origins, const floa
     const size_t hot_bytes = size_t(frozen->fz.hdr.hot_units) * 16u;
     const bool smem = !(flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= props.smem_optin / 2;
     const int grid = std::min(ublocks(n), props.sms * 8);
-    e = (flags & OM_RENDER_EXACT) ? om_exact::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0) : om_fast::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0);
+    e = !(flags & OM_RENDER_FAST_MATH) ? om_exact::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0) : om_fast::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "k_trace_rays failed: %s", cudaGetErrorString(e)));
     if (ids) e = cudaMemcpy(ids, a.ids, b_ids, cudaMemcpyDeviceToHost);

@@ -4,7 +4,9 @@
 // This header is compiled twice, into two namespaces:
 //   om_exact  (om_kernels_exact.cu, nvcc -fmad=false): no FMA contraction, IEEE div/sqrt, the
 //             reference's operation order -> bit-identical to the CPU oracle, sample by sample.
-//   om_fast   (om_kernels_fast.cu): the same expressions with FMA contraction.
+//             This is the DEFAULT build; explicit fmaf() is used only in culling code.
+//   om_fast   (om_kernels_fast.cu, OM_RENDER_FAST_MATH): the same expressions with FMA contraction
+//             everywhere; statistically equivalent, not bit-identical.
 // OM_NS and OM_EXACT are set by the including .cu file.
 #pragma once
 #include <cuda_runtime.h>
@@ -223,11 +225,28 @@ struct Counters {
     uint32_t segments, node_visits, prim_tests, sdf_evals, march_steps, normal_evals, march_entered;
 };
 
+// ---- culling arithmetic ----------------------------------------------------------------------
+// Box tests only decide what gets tested, never a result, and the boxes are padded (om_scene.cpp),
+// so they use explicit FMAs in BOTH builds (fmaf() is not subject to -fmad=false).
+struct RayInv {
+    V3 inv;    // 1/d, clamped to +-1e30 so an axis-parallel ray gives huge finite values, not inf - inf
+    V3 noinv;  // -o * inv
+};
+__device__ __forceinline__ float clamp_inv(float d) {
+    const float r = 1.f / d;
+    return copysignf(fminf(fabsf(r), 1e30f), d);
+}
+__device__ __forceinline__ RayInv ray_inv(const Ray& r) {
+    RayInv q;
+    q.inv = v3(clamp_inv(r.d.x), clamp_inv(r.d.y), clamp_inv(r.d.z));
+    q.noinv = v3(-r.o.x * q.inv.x, -r.o.y * q.inv.y, -r.o.z * q.inv.z);
+    return q;
+}
 // slab test of one box against the ray; returns entry distance, or +INF when missed
-__device__ __forceinline__ float slab(float lx, float ly, float lz, float hx, float hy, float hz, V3 inv, V3 oinv, float t_min, float t_max) {
-    const float ax = lx * inv.x - oinv.x, bx = hx * inv.x - oinv.x;
-    const float ay = ly * inv.y - oinv.y, by = hy * inv.y - oinv.y;
-    const float az = lz * inv.z - oinv.z, bz = hz * inv.z - oinv.z;
+__device__ __forceinline__ float slab(float lx, float ly, float lz, float hx, float hy, float hz, const RayInv& q, float t_min, float t_max) {
+    const float ax = fmaf(lx, q.inv.x, q.noinv.x), bx = fmaf(hx, q.inv.x, q.noinv.x);
+    const float ay = fmaf(ly, q.inv.y, q.noinv.y), by = fmaf(hy, q.inv.y, q.noinv.y);
+    const float az = fmaf(lz, q.inv.z, q.noinv.z), bz = fmaf(hz, q.inv.z, q.noinv.z);
     const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_max));
     return tn <= tf ? tn : kInf;
@@ -236,8 +255,7 @@ __device__ __forceinline__ float slab(float lx, float ly, float lz, float hx, fl
 template <bool SMEM, bool COUNT>
 __device__ __forceinline__ void traverse_bvh(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, Best& best, Counters& cn) {
     if (S.n_nodes == 0) return;
-    const V3 inv = v3(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
-    const V3 oinv = v3(r.o.x * inv.x, r.o.y * inv.y, r.o.z * inv.z);
+    const RayInv q = ray_inv(r);
     int2 stack[64];
     int sp = 0;
     int cur = 0;
@@ -246,8 +264,8 @@ __device__ __forceinline__ void traverse_bvh(const SceneView<SMEM>& sv, const Sc
         const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
         const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
         if (COUNT) cn.node_visits++;
-        const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, inv, oinv, t_min, best.t);
-        const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, inv, oinv, t_min, best.t);
+        const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, t_min, best.t);
+        const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, t_min, best.t);
         int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
         bool have;
         if (tl < kInf && tr < kInf) {
@@ -388,14 +406,10 @@ __device__ __forceinline__ void march(const SceneView<SMEM>& sv, const SceneHead
     // bounds can neither start within HIT_SIZE of a marched surface nor reach one: the
     // reference's loop would end without touching `rec`.  Skipping it is result-identical.
     {
-        const V3 inv = v3(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
-        const V3 oinv = v3(r.o.x * inv.x, r.o.y * inv.y, r.o.z * inv.z);
-        const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], inv, oinv, t_min, fminf(t_max, hit.t));
-        if (!(te < kInf)) {
-            // NaN rays reach here too (every comparison fails): the reference's unstuck() then
-            // finds no object (NaN < d is false) and returns the traced record unchanged.
-            return;
-        }
+        const RayInv q = ray_inv(r);
+        const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, t_min, fminf(t_max, hit.t));
+        if (!(te < kInf)) return;
+        // (a NaN ray passes this test and then finds no nearest object in unstuck(), like the reference)
     }
     if (COUNT) cn.march_entered++;
     const uint32_t n_ms = S.n[omd::PT_MSPHERE], n_mb = S.n[omd::PT_MBOX], n_mt = S.n[omd::PT_MTORUS];

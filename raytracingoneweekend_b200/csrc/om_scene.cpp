@@ -13,53 +13,73 @@ namespace {
 using omb::Aabb;
 const float kInf = std::numeric_limits<float>::infinity();
 
-// Pad a box so that every ray the f32 intersection routine reports as a hit also overlaps the
-// box: rounding in the primitive tests moves a reported hit by far less than this margin.
-Aabb padded(const double lo[3], const double hi[3]) {
+// Pad a box so that every ray the reference's f32 intersection routine reports as a hit also
+// overlaps the box.  `extra` is a per-axis world-space margin computed by the callers from the
+// routine's conditioning; on top of it comes a small relative margin for the slab arithmetic.
+Aabb padded(const double lo[3], const double hi[3], const double extra[3]) {
     Aabb b;
     for (int a = 0; a < 3; a++) {
         const double ext = hi[a] - lo[a];
         const double mag = std::max(std::fabs(lo[a]), std::fabs(hi[a]));
-        const double eps = 1e-4 * std::max(ext, mag) + 1e-5;
+        const double eps = 1e-4 * std::max(ext, mag) + 1e-5 + extra[a];
         b.lo[a] = nextafterf(float(lo[a] - eps), -kInf);
         b.hi[a] = nextafterf(float(hi[a] + eps), kInf);
     }
     return b;
 }
+double col_norm_min(const float* m) {  // smallest scale factor of the linear part (columns of R*S)
+    double best = 1e300;
+    for (int c = 0; c < 3; c++) best = std::min(best, std::sqrt(double(m[c]) * m[c] + double(m[4 + c]) * m[4 + c] + double(m[8 + c]) * m[8 + c]));
+    return std::max(best, 1e-30);
+}
 
 // traced.rs:65-70 boxes the unit sphere's +-1 cube; the exact extent of an ellipsoid M*S^2 along
 // axis i is the norm of row i of the linear part.
-Aabb sphere_box(const om_sphere& s) {
+// Sphere::hit (traced.rs:38-56) works in the sphere's local frame, where a ray origin `reach`
+// away sits at |o_l| = rho = reach / scale radii: `c = |o_l|^2 - 1` and `half_b^2 - a*c` then carry
+// an absolute f32 error of order rho^2 * 2^-23 against the "1", i.e. the test accepts rays that pass
+// within sqrt(1 + k*rho^2*2^-24) radii.  The box must contain that fattened sphere.
+Aabb sphere_box(const om_sphere& s, double reach) {
     const float* m = s.m_local_to_world;
-    double lo[3], hi[3];
+    const double rho = reach / col_norm_min(m);
+    const double fat = std::sqrt(1.0 + 32.0 * 5.96e-8 * rho * rho) - 1.0;
+    double lo[3], hi[3], extra[3];
     for (int i = 0; i < 3; i++) {
         const double h = std::sqrt(double(m[4 * i]) * m[4 * i] + double(m[4 * i + 1]) * m[4 * i + 1] + double(m[4 * i + 2]) * m[4 * i + 2]);
         lo[i] = m[4 * i + 3] - h;
         hi[i] = m[4 * i + 3] + h;
+        extra[i] = h * fat;
     }
-    return padded(lo, hi);
+    return padded(lo, hi, extra);
 }
-// traced.rs:301-304 uses +-1; the cube really spans +-0.5 (traced.rs:273-274)
-Aabb cube_box(const om_cube& s) {
+// traced.rs:301-304 uses +-1; the cube really spans +-0.5 (traced.rs:273-274).  A hit is accepted
+// when the computed local point is within 1e-5 of the surface (traced.rs:284); the computed point
+// itself is off by about rho * 2^-22 local units.
+Aabb cube_box(const om_cube& s, double reach) {
     const float* m = s.m_local_to_world;
-    double lo[3], hi[3];
+    const double rho = reach / col_norm_min(m);
+    const double fat = 2e-5 + rho * 1e-6;
+    double lo[3], hi[3], extra[3];
     for (int i = 0; i < 3; i++) {
         const double h = 0.5 * (std::fabs(double(m[4 * i])) + std::fabs(double(m[4 * i + 1])) + std::fabs(double(m[4 * i + 2])));
         lo[i] = m[4 * i + 3] - h;
         hi[i] = m[4 * i + 3] + h;
+        extra[i] = 2.0 * h * fat;
     }
-    return padded(lo, hi);
+    return padded(lo, hi, extra);
 }
-// traced.rs:208-219 is marked "may be wrong" in the reference; use the real vertices.
-Aabb bary_box(const om_barycentric& b, bool parallelogram) {
-    double lo[3], hi[3];
+// traced.rs:208-219 is marked "may be wrong" in the reference; use the real vertices.  The hit
+// point o + t*d is rounded at the scale of the ray's reach.
+Aabb bary_box(const om_barycentric& b, bool parallelogram, double reach) {
+    double lo[3], hi[3], extra[3];
     for (int i = 0; i < 3; i++) {
         const double o = b.origin[i], pu = o + double(b.u[i]) * b.u_length, pv = o + double(b.v[i]) * b.v_length;
         lo[i] = std::min(o, std::min(pu, pv));
         hi[i] = std::max(o, std::max(pu, pv));
         if (parallelogram) { const double puv = pu + double(b.v[i]) * b.v_length; lo[i] = std::min(lo[i], puv); hi[i] = std::max(hi[i], puv); }
+        extra[i] = reach * 4e-6;
     }
-    return padded(lo, hi);
+    return padded(lo, hi, extra);
 }
 double half_area(const Aabb& b) {
     const double dx = double(b.hi[0]) - b.lo[0], dy = double(b.hi[1]) - b.lo[1], dz = double(b.hi[2]) - b.lo[2];
@@ -84,7 +104,7 @@ void pack_material(Packer& p, const om_material& m, uint32_t pt, size_t index) {
 }
 }  // namespace
 
-void freeze(const omh::SceneLists& L, uint32_t flags, FrozenScene& out) {
+void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, FrozenScene& out) {
     using namespace omd;
     SceneHeader& h = out.hdr;
     memset(&h, 0, sizeof h);
@@ -99,12 +119,38 @@ void freeze(const omh::SceneLists& L, uint32_t flags, FrozenScene& out) {
     for (int i = 0; i < 8; i++) out.n_total += h.n[i];
 
     // ---- bounded traced primitives -> BVH; unbounded / scene-sized ones -> always-test list ----
+    // `reach`: how far a ray origin can be from an object it still has to find.  Origins are the
+    // camera or points on other objects, so the diagonal of everything scene-sized objects aside,
+    // and at least the reference's t_max of 100 (main.rs:206).
+    double reach = 100.0;
+    {
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        auto grow_pt = [&](double x, double y, double z, double r) {
+            const double p[3] = {x, y, z};
+            for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a] - r); hi[a] = std::max(hi[a], p[a] + r); }
+        };
+        std::vector<double> radii;
+        for (const om_sphere& o : L.spheres) radii.push_back(col_norm_min(o.m_local_to_world));
+        double med = 0.0;
+        if (!radii.empty()) { std::vector<double> t = radii; std::nth_element(t.begin(), t.begin() + t.size() / 2, t.end()); med = t[t.size() / 2]; }
+        for (size_t i = 0; i < L.spheres.size(); i++)
+            if (L.spheres.size() < 4 || radii[i] <= 64.0 * med) grow_pt(L.spheres[i].m_local_to_world[3], L.spheres[i].m_local_to_world[7], L.spheres[i].m_local_to_world[11], radii[i]);
+        for (const om_cube& o : L.cubes) grow_pt(o.m_local_to_world[3], o.m_local_to_world[7], o.m_local_to_world[11], 1.0);
+        for (const om_barycentric& o : L.triangles) grow_pt(o.origin[0], o.origin[1], o.origin[2], std::max(o.u_length, o.v_length));
+        for (const om_barycentric& o : L.parallelograms) grow_pt(o.origin[0], o.origin[1], o.origin[2], double(o.u_length) + o.v_length);
+        if (cam) grow_pt(cam->origin[0], cam->origin[1], cam->origin[2], 0.0);
+        if (lo[0] <= hi[0]) {
+            const double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+            const double diag = std::sqrt(dx * dx + dy * dy + dz * dz);
+            if (std::isfinite(diag)) reach = std::max(reach, diag);
+        }
+    }
     std::vector<uint32_t> refs;
     std::vector<Aabb> boxes;
-    for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i])); }
-    for (size_t i = 0; i < L.cubes.size(); i++) { refs.push_back(make_ref(PT_CUBE, uint32_t(i))); boxes.push_back(cube_box(L.cubes[i])); }
-    for (size_t i = 0; i < L.triangles.size(); i++) { refs.push_back(make_ref(PT_TRI, uint32_t(i))); boxes.push_back(bary_box(L.triangles[i], false)); }
-    for (size_t i = 0; i < L.parallelograms.size(); i++) { refs.push_back(make_ref(PT_PARA, uint32_t(i))); boxes.push_back(bary_box(L.parallelograms[i], true)); }
+    for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i], reach)); }
+    for (size_t i = 0; i < L.cubes.size(); i++) { refs.push_back(make_ref(PT_CUBE, uint32_t(i))); boxes.push_back(cube_box(L.cubes[i], reach)); }
+    for (size_t i = 0; i < L.triangles.size(); i++) { refs.push_back(make_ref(PT_TRI, uint32_t(i))); boxes.push_back(bary_box(L.triangles[i], false, reach)); }
+    for (size_t i = 0; i < L.parallelograms.size(); i++) { refs.push_back(make_ref(PT_PARA, uint32_t(i))); boxes.push_back(bary_box(L.parallelograms[i], true, reach)); }
     std::vector<uint32_t> large;
     for (size_t i = 0; i < L.infinite_planes.size(); i++) large.push_back(make_ref(PT_PLANE, uint32_t(i)));  // Bounded default: +-INF (bounding_box.rs:69-73)
     if (!(flags & 1u) && refs.size() > 4) {

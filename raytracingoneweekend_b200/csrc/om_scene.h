@@ -16,6 +16,7 @@ struct FrozenScene {
 };
 
 // flags: bit 0 = put every bounded primitive in the BVH even when it is scene-sized
-void freeze(const omh::SceneLists& lists, uint32_t flags, FrozenScene& out);
+// cam (may be NULL) only widens the numerical margins of the boxes; it never changes a result.
+void freeze(const omh::SceneLists& lists, const om_camera* cam, uint32_t flags, FrozenScene& out);
 
 }  // namespace oms

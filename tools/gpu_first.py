@@ -27,7 +27,7 @@ orig = np.tile(np.array([13, 2, 3], np.float32), (n, 1)) + rng.normal(0, 0.5, (n
 tgt = rng.uniform(-6, 6, (n, 3)).astype(np.float32); tgt[:, 1] = rng.uniform(0, 1.5, n)
 dirs = tgt - orig
 oi, ot, op, on = osc.trace_rays(orig, dirs)
-for name, fl in [("exact_bvh", A.RENDER_EXACT), ("exact_brute", A.RENDER_EXACT | A.RENDER_BRUTE_FORCE), ("exact_bvh_global", A.RENDER_EXACT | A.RENDER_NO_SMEM_SCENE), ("fast_bvh", 0)]:
+for name, fl in [("exact_bvh", 0), ("exact_brute", A.RENDER_BRUTE_FORCE), ("exact_bvh_global", A.RENDER_NO_SMEM_SCENE), ("fast_bvh", A.RENDER_FAST_MATH)]:
     gi, gt, gp, gn = fz.hit(orig, dirs, flags=fl)
     same_t = (gt.view(np.uint32) == ot.view(np.uint32))
     print(name, "ids equal", (gi == oi).mean(), "t bit-equal", same_t.mean(), "points bit-equal", (gp.view(np.uint32) == op.view(np.uint32)).all(1).mean(),
@@ -41,7 +41,7 @@ for name, fl in [("exact_bvh", A.RENDER_EXACT), ("exact_brute", A.RENDER_EXACT |
 # ---- image parity (exact), 96x64x8spp
 W, H, SPP = 96, 64, 8
 for flags_extra, label in [(0, "fixed"), (A.RENDER_ADAPTIVE, "adaptive")]:
-    p = api.render_params(W, H, SPP if not flags_extra else 64, seed=7, flags=A.RENDER_EXACT | flags_extra)
+    p = api.render_params(W, H, SPP if not flags_extra else 64, seed=7, flags=flags_extra)
     t0 = time.time(); ro = osc.render(cam, p); t1 = time.time()
     r = api.Renderer(fz, cam, p); r.launch(0); r.sync(); g = r.read_pixels()
     o = ro["pixels"]
@@ -54,7 +54,7 @@ for flags_extra, label in [(0, "fixed"), (A.RENDER_ADAPTIVE, "adaptive")]:
     r.close()
 
 # ---- primary ids
-p = api.render_params(300, 200, 4, seed=3, flags=A.RENDER_EXACT)
+p = api.render_params(300, 200, 4, seed=3, flags=0)
 r = api.Renderer(fz, cam, p)
 for mode in (0, 1):
     gi, gt = r.primary(mode, 2); oi2, ot2 = osc.primary(cam, p, mode, 2)
@@ -84,7 +84,7 @@ def bench(label, fz, cam, W, H, spp, flags=0, reps=2):
 cam169 = api.Camera.new((13, 2, 3), (0, 0, 0), (0, 1, 0), 20., 16 / 9, 0.1, 10.)
 bench("C1_fast", fz, cam, 1200, 800, 10)
 bench("C1_fast_counters", fz, cam, 1200, 800, 10, A.RENDER_COUNTERS)
-bench("C1_exact", fz, cam, 1200, 800, 10, A.RENDER_EXACT)
+bench("C1_exact", fz, cam, 1200, 800, 10, 0)
 bench("C1_fast_global", fz, cam, 1200, 800, 10, A.RENDER_NO_SMEM_SCENE)
 bench("C1_fast_brute", fz, cam, 1200, 800, 10, A.RENDER_BRUTE_FORCE, reps=1)
 bench("C2_fast_64spp", fz, cam169, 1920, 1080, 64)
