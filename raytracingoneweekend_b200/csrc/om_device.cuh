@@ -45,8 +45,10 @@ struct Rng {
     uint32_t k0, k1, a, b, draw;
     uint32_t b0, b1, b2, b3;
 };
-__device__ __forceinline__ void philox_block(Rng& g) {
-    uint32_t c0 = g.draw >> 2, c1 = g.a, c2 = g.b, c3 = 0u /* STREAM_PATH */, k0 = g.k0, k1 = g.k1;
+// Out of line on purpose: ~90 instructions that every draw site would otherwise inline (the first
+// kernels were > 100 KB of SASS and stalled on instruction fetch).  Values travel in registers.
+__device__ __noinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
+    uint32_t c3 = 0u;  // STREAM_PATH
 #pragma unroll
     for (int r = 0; r < 10; r++) {
         const uint32_t lo0 = 0xD2511F53u * c0, hi0 = __umulhi(0xD2511F53u, c0);
@@ -54,7 +56,11 @@ __device__ __forceinline__ void philox_block(Rng& g) {
         c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
-    g.b0 = c0; g.b1 = c1; g.b2 = c2; g.b3 = c3;
+    return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ void philox_block(Rng& g) {
+    const uint4 b = philox4x32_10(g.draw >> 2, g.a, g.b, g.k0, g.k1);
+    g.b0 = b.x; g.b1 = b.y; g.b2 = b.z; g.b3 = b.w;
 }
 __device__ __forceinline__ void rng_init(Rng& g, uint32_t k0, uint32_t k1, uint32_t pixel, uint32_t sample) {
     g.k0 = k0; g.k1 = k1; g.a = pixel; g.b = sample; g.draw = 0;
@@ -252,72 +258,86 @@ __device__ __forceinline__ float slab(float lx, float ly, float lz, float hx, fl
     return tn <= tf ? tn : kInf;
 }
 
-template <bool SMEM, bool COUNT>
-__device__ __forceinline__ void traverse_bvh(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, Best& best, Counters& cn) {
-    if (S.n_nodes == 0) return;
-    const RayInv q = ray_inv(r);
-    int2 stack[64];
-    int sp = 0;
-    int cur = 0;
-    for (;;) {
-        // cur >= 0: inner node
-        const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
-        const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
-        if (COUNT) cn.node_visits++;
-        const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, t_min, best.t);
-        const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, t_min, best.t);
-        int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
-        bool have;
-        if (tl < kInf && tr < kInf) {
-            int nearc = cl, farc = cr;
-            float tfar = tr;
-            if (tr < tl) { nearc = cr; farc = cl; tfar = tl; }
-            if (sp < 64) { stack[sp] = make_int2(farc, __float_as_int(tfar)); sp++; }
-            cur = nearc;
-            have = true;
-        } else if (tl < kInf) { cur = cl; have = true; }
-        else if (tr < kInf) { cur = cr; have = true; }
-        else have = false;
-        for (;;) {
-            if (have) {
-                if (cur >= 0) break;  // inner node: continue the outer loop
-                if (COUNT) cn.prim_tests++;
-                test_prim(sv, S, (uint32_t)(~cur), r, t_min, best);
-            }
-            // pop
-            have = false;
-            while (sp > 0) {
-                sp--;
-                const int2 e = stack[sp];
-                if (__int_as_float(e.y) <= best.t) { cur = e.x; have = true; break; }
-            }
-            if (!have) return;
-        }
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int STACK_DEPTH = 64;
+
+// k-th entry of the linear part of a query: the always-test list (infinite planes, scene-sized
+// objects), or in brute-force mode every traced primitive in the reference's scan order.
+template <bool SMEM>
+__device__ __forceinline__ uint32_t linear_ref(const SceneView<SMEM>& sv, const SceneHeader& S, bool brute, uint32_t k) {
+    if (brute) {
+        uint32_t type = 0;
+        while (type < 4u && k >= S.n[type]) { k -= S.n[type]; type++; }
+        return omd::make_ref(type, k);
     }
+    const float4 q = sv.hot(S.off_large + (k >> 2));
+    const uint32_t sel = k & 3u;
+    return __float_as_uint(sel == 0 ? q.x : (sel == 1 ? q.y : (sel == 2 ? q.z : q.w)));
 }
 
-// FrozenHittableList::hit, traced part (hits.rs:270-286)
+// FrozenHittableList::hit, traced part (hits.rs:270-286), for a whole warp at once.
+//
+// Every lane walks its own ray through a list of ITEMS: first the linear entries, then the BVH
+// (inner node = box pair, leaf = primitive).  A lane's next item is either an inner node or a
+// leaf; each iteration the warp VOTES and runs only the kind that more lanes are waiting for, so
+// the two bodies always execute with at least half of the busy lanes active (the first version
+// tested a leaf the moment a lane reached it: ~2 lanes active, half of all issue slots).
+// All 32 lanes must call this; `alive` says whether the lane has a ray.
 template <bool SMEM, bool COUNT>
-__device__ __forceinline__ Best closest_traced(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, Counters& cn) {
+__device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute,
+                                                    bool alive, Counters& cn, int2* stack) {
     Best best;
     best.t = t_max;
     best.ref = omd::REF_NONE;
-    if (brute) {
-        for (uint32_t type = 0; type < 5; type++)
-            for (uint32_t i = 0; i < S.n[type]; i++) {
-                if (COUNT) cn.prim_tests++;
-                test_prim(sv, S, omd::make_ref(type, i), r, t_min, best);
+    const uint32_t n_lin = brute ? (S.n[0] + S.n[1] + S.n[2] + S.n[3] + S.n[4]) : S.n_large;
+    const bool have_bvh = !brute && S.n_nodes > 0u;
+    const RayInv q = ray_inv(r);
+    uint32_t k = 0;
+    int sp = 0, cur = 0;
+    bool act = alive, in_bvh = false;
+    // take the next item after a leaf (or at the start): linear entries, then the BVH root, then the stack
+    auto pop = [&]() {
+        while (sp > 0) {
+            sp--;
+            const int2 e = stack[sp];
+            if (__int_as_float(e.y) <= best.t) { cur = e.x; return; }
+        }
+        act = false;
+    };
+    auto next_item = [&]() {
+        if (k < n_lin) { cur = ~(int)linear_ref(sv, S, brute, k); k++; return; }
+        if (!in_bvh) { in_bvh = true; if (have_bvh) { cur = 0; return; } }
+        pop();
+    };
+    if (act) next_item();
+    for (;;) {
+        const unsigned m_inner = __ballot_sync(FULL, act && cur >= 0);
+        const unsigned m_leaf = __ballot_sync(FULL, act && cur < 0);
+        if ((m_inner | m_leaf) == 0u) break;
+        if (__popc(m_inner) >= __popc(m_leaf)) {
+            if (act && cur >= 0) {
+                const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
+                const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
+                if (COUNT) cn.node_visits++;
+                const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, t_min, best.t);
+                const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, t_min, best.t);
+                const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
+                if (tl < kInf && tr < kInf) {
+                    const bool right_first = tr < tl;
+                    if (sp < STACK_DEPTH) { stack[sp] = make_int2(right_first ? cl : cr, __float_as_int(right_first ? tl : tr)); sp++; }
+                    cur = right_first ? cr : cl;
+                } else if (tl < kInf) cur = cl;
+                else if (tr < kInf) cur = cr;
+                else pop();
             }
-        return best;
+        } else {
+            if (act && cur < 0) {
+                if (COUNT) cn.prim_tests++;
+                test_prim(sv, S, (uint32_t)(~cur), r, t_min, best);
+                next_item();
+            }
+        }
     }
-    for (uint32_t k = 0; k < S.n_large; k++) {
-        const float4 q = sv.hot(S.off_large + (k >> 2));
-        const uint32_t sel = k & 3u;
-        const uint32_t ref = __float_as_uint(sel == 0 ? q.x : (sel == 1 ? q.y : (sel == 2 ? q.z : q.w)));
-        if (COUNT) cn.prim_tests++;
-        test_prim(sv, S, ref, r, t_min, best);
-    }
-    traverse_bvh<SMEM, COUNT>(sv, S, r, t_min, best, cn);
     return best;
 }
 
@@ -370,9 +390,11 @@ __device__ __forceinline__ V3 numeric_local_normal(V3 p, LSDF lsdf) {
     const float sign = (end_val > start_val) ? 1.f : -1.f;
     return normal * sign;
 }
-// Marched::get_outward_normal (marched.rs:19-24; MarchedSphere override :60-63)
+// Marched::get_outward_normal (marched.rs:19-24; MarchedSphere override :60-63).  Out of line: it
+// runs once per marched HIT, not per step (see march()).
 template <bool SMEM>
-__device__ __forceinline__ V3 marched_normal(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t type, uint32_t i, V3 p) {
+__device__ __noinline__ V3 marched_normal(SceneView<SMEM> sv, const SceneHeader& S, uint32_t ref, V3 p) {
+    const uint32_t type = omd::ref_type(ref), i = omd::ref_index(ref);
     if (type == omd::PT_MSPHERE) {
         const float4 cr = sv.hot(S.off_hot[omd::PT_MSPHERE] + omd::U_MSPHERE * i);
         return om::unit(p - v3(cr.x, cr.y, cr.z));
@@ -393,86 +415,115 @@ __device__ __forceinline__ V3 marched_normal(const SceneView<SMEM>& sv, const Sc
     }
 }
 
+// j-th marched object in the reference's order: spheres, boxes, tori (hits.rs:301-311)
+__device__ __forceinline__ uint32_t marched_ref(const SceneHeader& S, uint32_t j) {
+    const uint32_t n_ms = S.n[omd::PT_MSPHERE], n_mb = S.n[omd::PT_MBOX];
+    if (j < n_ms) return omd::make_ref(omd::PT_MSPHERE, j);
+    if (j < n_ms + n_mb) return omd::make_ref(omd::PT_MBOX, j - n_ms);
+    return omd::make_ref(omd::PT_MTORUS, j - n_ms - n_mb);
+}
+struct Near {
+    float d;       // min over the marched objects of |sdf(p)|
+    uint32_t ref;  // the first object that attains it (strict `<`, hits.rs:304,345); REF_NONE if none
+};
+template <bool SMEM>
+__device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p) {
+    Near n;
+    n.d = kInf;
+    n.ref = omd::REF_NONE;
+    for (uint32_t j = 0; j < S.n_marched; j++) {
+        const uint32_t ref = marched_ref(S, j);
+        const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+        if (d < n.d) { n.d = d; n.ref = ref; }
+    }
+    return n;
+}
+template <bool SMEM>
+__device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& S, uint32_t ref, V3 p) {
+    return fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+}
+
 struct Hit {
     float t;
     uint32_t ref;  // REF_NONE = miss
     V3 point, normal;  // filled for marched hits only
 };
 
-// FrozenHittableList::hit, marched part (hits.rs:288-332) + unstuck (hits.rs:336-365)
+// FrozenHittableList::hit, marched part (hits.rs:288-332) + unstuck (hits.rs:336-365).
+// `closest` is the traced hit distance (or t_max).  Returns ref == REF_NONE when the march ends
+// without a hit (the traced record stands).
 template <bool SMEM, bool COUNT>
-__device__ __forceinline__ void march(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, Hit& hit, Counters& cn) {
-    // A ray whose [t_min, min(t_max, closest)] span misses the padded union of the marched
-    // bounds can neither start within HIT_SIZE of a marched surface nor reach one: the
-    // reference's loop would end without touching `rec`.  Skipping it is result-identical.
-    {
-        const RayInv q = ray_inv(r);
-        const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, t_min, fminf(t_max, hit.t));
-        if (!(te < kInf)) return;
-        // (a NaN ray passes this test and then finds no nearest object in unstuck(), like the reference)
-    }
-    if (COUNT) cn.march_entered++;
-    const uint32_t n_ms = S.n[omd::PT_MSPHERE], n_mb = S.n[omd::PT_MBOX], n_mt = S.n[omd::PT_MTORUS];
+__device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, Counters* cn) {
+    Hit out;
+    out.t = closest;
+    out.ref = omd::REF_NONE;
+    out.point = v3(0.f, 0.f, 0.f);
+    out.normal = v3(0.f, 0.f, 0.f);
+    if (COUNT) cn->march_entered++;
     // ---- unstuck ----
     float t;
     {
         const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
         float new_t = t_min;
-        float d = kInf;
-        const V3 p = ray_at(r, t_min);
-        uint32_t mtype = 0xFFFFFFFFu, mi = 0;
-        for (uint32_t i = 0; i < n_ms; i++) { const float nd = fabsf(marched_sdf(sv, S, omd::PT_MSPHERE, i, p)); if (nd < d) { d = nd; mtype = omd::PT_MSPHERE; mi = i; } }
-        for (uint32_t i = 0; i < n_mb; i++) { const float nd = fabsf(marched_sdf(sv, S, omd::PT_MBOX, i, p)); if (nd < d) { d = nd; mtype = omd::PT_MBOX; mi = i; } }
-        for (uint32_t i = 0; i < n_mt; i++) { const float nd = fabsf(marched_sdf(sv, S, omd::PT_MTORUS, i, p)); if (nd < d) { d = nd; mtype = omd::PT_MTORUS; mi = i; } }
-        if (COUNT) cn.sdf_evals += n_ms + n_mb + n_mt;
-        if (mtype == 0xFFFFFFFFu) return;  // `marched.is_none()` -> INF -> return rec
-        float aux = d;
+        const Near n0 = nearest_marched(sv, S, ray_at(r, t_min));
+        if (COUNT) cn->sdf_evals += S.n_marched;
+        if (n0.ref == omd::REF_NONE) return out;  // `marched.is_none()` -> INF -> return rec (also every NaN ray)
+        float aux = n0.d;
         int steps = 0;
         while (aux < HIT_SIZE && steps < UNSTUCK_MAX_STEPS) {
             new_t += MIN_STEP_SIZE;
-            aux = fabsf(marched_sdf(sv, S, mtype, mi, ray_at(r, new_t)));
+            aux = abs_sdf_of(sv, S, n0.ref, ray_at(r, new_t));
             steps++;
-            if (COUNT) cn.sdf_evals++;
+            if (COUNT) cn->sdf_evals++;
         }
         t = new_t;
     }
     // ---- sphere tracing ----
     int max_march_iter = 1024;
-    while (t < t_max && t < hit.t && max_march_iter > 0) {
+    while (t < t_max && t < closest && max_march_iter > 0) {
         max_march_iter--;
         const V3 point = ray_at(r, t);
-        float distance = kInf;
-        uint32_t mtype = 0xFFFFFFFFu, mi = 0;
-        for (uint32_t i = 0; i < n_ms; i++) { const float d = fabsf(marched_sdf(sv, S, omd::PT_MSPHERE, i, point)); if (d < distance) { distance = d; mtype = omd::PT_MSPHERE; mi = i; } }
-        for (uint32_t i = 0; i < n_mb; i++) { const float d = fabsf(marched_sdf(sv, S, omd::PT_MBOX, i, point)); if (d < distance) { distance = d; mtype = omd::PT_MBOX; mi = i; } }
-        for (uint32_t i = 0; i < n_mt; i++) { const float d = fabsf(marched_sdf(sv, S, omd::PT_MTORUS, i, point)); if (d < distance) { distance = d; mtype = omd::PT_MTORUS; mi = i; } }
-        if (COUNT) { cn.march_steps++; cn.sdf_evals += n_ms + n_mb + n_mt; }
-        if (mtype == 0xFFFFFFFFu) return;  // `material.is_none()`
-        if (distance < HIT_SIZE) {
+        const Near n = nearest_marched(sv, S, point);
+        if (COUNT) { cn->march_steps++; cn->sdf_evals += S.n_marched; }
+        if (n.ref == omd::REF_NONE) return out;  // `material.is_none()`
+        if (n.d < HIT_SIZE) {
             // The reference evaluates the normal of the nearest object at every step
             // (hits.rs:306); only the value at the accepted point survives, so it is computed here.
-            hit.t = t;
-            hit.ref = omd::make_ref(mtype, mi);
-            hit.point = point;
-            hit.normal = marched_normal(sv, S, mtype, mi, point);
-            if (COUNT) cn.normal_evals++;
-            return;
+            out.t = t;
+            out.ref = n.ref;
+            out.point = point;
+            out.normal = marched_normal(sv, S, n.ref, point);
+            if (COUNT) cn->normal_evals++;
+            return out;
         }
-        t += distance;
+        t += n.d;
     }
+    return out;
 }
 
-// FrozenHittableList::hit (hits.rs:270-334); also first_hit (the BVH subsumes CameraHash)
+// FrozenHittableList::hit (hits.rs:270-334); also first_hit (the BVH subsumes CameraHash).
+// Warp-collective: all 32 lanes call it, `alive` marks the lanes that carry a ray.
 template <bool SMEM, bool COUNT>
-__device__ __forceinline__ Hit closest_hit(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, Counters& cn) {
-    if (COUNT) cn.segments++;
-    const Best b = closest_traced<SMEM, COUNT>(sv, S, r, t_min, t_max, brute, cn);
+__device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, bool alive,
+                                                Counters& cn, int2* stack) {
+    if (COUNT && alive) cn.segments++;
+    const Best b = closest_traced_warp<SMEM, COUNT>(sv, S, r, t_min, t_max, brute, alive, cn, stack);
     Hit h;
     h.t = b.t;
     h.ref = b.ref;
     h.point = v3(0.f, 0.f, 0.f);
     h.normal = v3(0.f, 0.f, 0.f);
-    if (S.n_marched) march<SMEM, COUNT>(sv, S, r, t_min, t_max, h, cn);
+    if (S.n_marched != 0u && alive) {
+        // A ray whose [t_min, min(t_max, closest)] span misses the padded union of the marched
+        // bounds can neither start within HIT_SIZE of a marched surface nor reach one: the
+        // reference's loop would end without touching `rec`.  Skipping it is result-identical.
+        const RayInv q = ray_inv(r);
+        const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, t_min, fminf(t_max, h.t));
+        if (te < kInf) {
+            const Hit m = march<SMEM, COUNT>(sv, S, r, t_min, t_max, h.t, &cn);
+            if (m.ref != omd::REF_NONE) h = m;
+        }
+    }
     return h;
 }
 
@@ -552,17 +603,19 @@ __device__ __forceinline__ float reflectance(float cosv, float ref_idx) {  // :1
 // Material::scatter (:39-95).  Returns the attenuation; `r` becomes the scattered ray.
 __device__ __forceinline__ V3 scatter(const Material& m, Ray& r, V3 point, V3 normal, Rng& g) {
     V3 new_dir, att;
-    if (m.mat_type == OM_MAT_LAMBERTIAN) {
-        new_dir = normal + om::unit(rand_in_unit_sphere(g));
-        const float eps = 1e-8f;
-        if (fabsf(new_dir.x) < eps && fabsf(new_dir.y) < eps && fabsf(new_dir.z) < eps) new_dir = normal;
+    if (m.mat_type != OM_MAT_DIELECTRIC) {
+        // Lambertian (:52-61) and Metal (:62-66, no absorb test) both start their draws with
+        // rand_in_unit_sphere (metal even when fuzz == 0): one shared rejection loop.
+        const V3 s = rand_in_unit_sphere(g);
+        if (m.mat_type == OM_MAT_LAMBERTIAN) {
+            new_dir = normal + om::unit(s);
+            const float eps = 1e-8f;
+            if (fabsf(new_dir.x) < eps && fabsf(new_dir.y) < eps && fabsf(new_dir.z) < eps) new_dir = normal;
+        } else {
+            new_dir = reflect(r.d, normal) + m.fuzz * s;
+        }
         att = m.albedo;
-    } else if (m.mat_type == OM_MAT_METAL) {
-        const V3 reflected = reflect(r.d, normal);
-        const V3 s = rand_in_unit_sphere(g);  // drawn even when fuzz == 0
-        new_dir = reflected + m.fuzz * s;
-        att = m.albedo;
-    } else {
+    } else {  // :68-95
         const V3 dir_unit = r.d;
         const bool front_face = om::dot(dir_unit, normal) < 0.f;
         const float refraction_ratio = front_face ? 1.0f / m.ior : m.ior;
@@ -713,41 +766,49 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_render(const __grid_constant
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
     unsigned long long credited = 0, traced = 0;
     const uint32_t lane = threadIdx.x & 31u;
+    int2 stack[STACK_DEPTH];
+    const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;  // segment 0 + `for _i in 1..depth`
 
     for (;;) {
         // one ticket = one warp-sized run of 32 work slots (an 8x4 pixel tile)
         uint32_t ticket = 0;
         if (lane == 0u) ticket = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], 1ull);
-        ticket = __shfl_sync(0xffffffffu, ticket, 0);
+        ticket = __shfl_sync(FULL, ticket, 0);
         const uint32_t base = ticket * 32u;
         if (base >= A.n_work) break;
         const uint32_t k = base + lane;
         const uint32_t pxl = k < A.n_work ? work_to_pixel(A, k) : 0xFFFFFFFFu;
-        if (pxl == 0xFFFFFFFFu) continue;
+        const bool valid = pxl != 0xFFFFFFFFu;
 
         // ---- load Stats ----
         Stats st;
-        {
+        st.sum = v3(0.f, 0.f, 0.f); st.n = 0; st.avg_depth = 0.f; st.bad_avgs = 0; st.bloom_lo = 0; st.bloom_hi = 0; st.color = 0;
+        uint32_t todo = 0;
+        if (valid) {
             const float4 a = A.acc[pxl];
             const uint4 x = A.aux[pxl];
             st.sum = v3(a.x, a.y, a.z); st.n = __float_as_uint(a.w);
             st.avg_depth = __uint_as_float(x.x); st.bad_avgs = x.y; st.bloom_lo = x.z; st.bloom_hi = x.w;
             st.color = stats_color_of(st.sum, st.n);
+            todo = A.spp_budget > st.n ? min(A.spp_budget - st.n, A.spp_pass) : 0u;
+            if (adaptive && st.bad_avgs >= 5u) todo = 0u;
         }
-        uint32_t todo = A.spp_budget > st.n ? min(A.spp_budget - st.n, A.spp_pass) : 0u;
-        if (adaptive && st.bad_avgs >= 5u) todo = 0u;
+        const bool touched = todo > 0u;
 
-        // ---- per-lane path state machine ----
+        // ---- per-lane path state machine; the loop itself is warp-uniform ----
         Rng g;
+        rng_init(g, A.seed_lo, A.seed_hi, 0u, 0u);
+        g.b0 = g.b1 = g.b2 = g.b3 = 0u;
         Ray ray;
+        ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
         V3 color = v3(1.f, 1.f, 1.f);
         uint32_t seg = 0;
         float first_t = kInf;
         uint32_t first_lo = 0, first_hi = 0;
-        const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;  // segment 0 + `for _i in 1..depth`
         bool fresh = true;
-        while (todo > 0u) {
-            if (fresh) {
+        while (__any_sync(FULL, todo > 0u)) {
+            const bool alive = todo > 0u;
+            if (alive && fresh) {
                 const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
                 rng_init(g, A.seed_lo, A.seed_hi, pxl, sample);
                 ray = primary_ray(A, pxl, sample, g);
@@ -755,43 +816,47 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_render(const __grid_constant
                 seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
                 fresh = false;
             }
-            Hit h = closest_hit<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, cn);
-            bool finished;
-            V3 result = color;
-            if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
-                finish_hit(sv, S, ray, A.tmin, h);
-                const Material m = load_material(sv, S, h.ref);
-                if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
-                color = color * scatter(m, ray, h.point, h.normal, g);
-                seg++;
-                finished = seg >= nseg;
-                if (finished) result = -v3(0.f, 0.f, 0.f);  // out of depth: -black (:142)
-            } else {  // None: sky (:117-123)
-                const float t = 0.5f * (ray.d.y + 1.0f);
-                const V3 sky = (1.0f - t) * v3(1.f, 1.f, 1.f) + t * v3(0.5f, 0.7f, 1.0f);
-                result = color * sky;
-                finished = true;
-            }
-            if (finished) {
-                bool done = stats_add(st, result, first_t, first_lo, first_hi);
-                if (!adaptive) done = false;
-                traced++;
-                todo--;
-                const uint32_t left = A.spp_budget - st.n;
-                credited += (done ? (unsigned long long)left : 0ull) + 1ull;  // render_thread.rs:196-198
-                if (done) todo = 0u;
-                fresh = true;
+            Hit h = closest_hit_warp<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
+            if (alive) {
+                bool finished;
+                V3 result = color;
+                if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
+                    finish_hit(sv, S, ray, A.tmin, h);
+                    const Material m = load_material(sv, S, h.ref);
+                    if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
+                    color = color * scatter(m, ray, h.point, h.normal, g);
+                    seg++;
+                    finished = seg >= nseg;
+                    if (finished) result = -v3(0.f, 0.f, 0.f);  // out of depth: -black (:142)
+                } else {  // None: sky (:117-123)
+                    const float t = 0.5f * (ray.d.y + 1.0f);
+                    const V3 sky = (1.0f - t) * v3(1.f, 1.f, 1.f) + t * v3(0.5f, 0.7f, 1.0f);
+                    result = color * sky;
+                    finished = true;
+                }
+                if (finished) {
+                    bool done = stats_add(st, result, first_t, first_lo, first_hi);
+                    if (!adaptive) done = false;
+                    traced++;
+                    todo--;
+                    const uint32_t left = A.spp_budget - st.n;
+                    credited += (done ? (unsigned long long)left : 0ull) + 1ull;  // render_thread.rs:196-198
+                    if (done) todo = 0u;
+                    fresh = true;
+                }
             }
         }
         // ---- store Stats ----
-        A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
-        A.aux[pxl] = make_uint4(__float_as_uint(st.avg_depth), st.bad_avgs, st.bloom_lo, st.bloom_hi);
+        if (touched) {
+            A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
+            A.aux[pxl] = make_uint4(__float_as_uint(st.avg_depth), st.bad_avgs, st.bloom_lo, st.bloom_hi);
+        }
     }
 
     // ---- progress counters: warp-aggregate, one atomic per warp ----
     for (int o = 16; o > 0; o >>= 1) {
-        credited += __shfl_xor_sync(0xffffffffu, credited, o);
-        traced += __shfl_xor_sync(0xffffffffu, traced, o);
+        credited += __shfl_xor_sync(FULL, credited, o);
+        traced += __shfl_xor_sync(FULL, traced, o);
     }
     if ((threadIdx.x & 31) == 0) {
         if (credited) atomicAdd(&A.counters[CTR_CREDITED], credited);
@@ -817,13 +882,22 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_primary(const __grid_constan
     sv.hot_g = A.hot_g;
     sv.cold_g = A.cold_g;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
-    for (uint32_t pxl = blockIdx.x * CTA_THREADS + threadIdx.x; pxl < A.npx; pxl += gridDim.x * CTA_THREADS) {
+    int2 stack[STACK_DEPTH];
+    // warp-uniform trip count: closest_hit_warp is a warp-collective
+    for (uint32_t base = blockIdx.x * CTA_THREADS; base < A.npx; base += gridDim.x * CTA_THREADS) {
+        const uint32_t pxl = base + threadIdx.x;
+        const bool alive = pxl < A.npx;
         Ray ray;
-        if (mode == 0u) ray = center_ray(A, pxl);
-        else { Rng g; rng_init(g, A.seed_lo, A.seed_hi, pxl, sample_index); ray = primary_ray(A, pxl, sample_index, g); }
-        const Hit h = closest_hit<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, cn);
-        if (h.ref == omd::REF_NONE) { ids[pxl] = 0ull; tout[pxl] = kInf; }
-        else { ids[pxl] = ((unsigned long long)(omd::ref_type(h.ref) + 1u) << 32) | (unsigned long long)(omd::ref_index(h.ref) + 1u); tout[pxl] = h.t; }
+        ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
+        if (alive) {
+            if (mode == 0u) ray = center_ray(A, pxl);
+            else { Rng g; rng_init(g, A.seed_lo, A.seed_hi, pxl, sample_index); ray = primary_ray(A, pxl, sample_index, g); }
+        }
+        const Hit h = closest_hit_warp<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
+        if (alive) {
+            if (h.ref == omd::REF_NONE) { ids[pxl] = 0ull; tout[pxl] = kInf; }
+            else { ids[pxl] = ((unsigned long long)(omd::ref_type(h.ref) + 1u) << 32) | (unsigned long long)(omd::ref_index(h.ref) + 1u); tout[pxl] = h.t; }
+        }
     }
 }
 
@@ -835,11 +909,18 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_trace_rays(const __grid_cons
     sv.hot_g = A.hot_g;
     sv.cold_g = A.cold_g;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
-    for (uint32_t i = blockIdx.x * CTA_THREADS + threadIdx.x; i < A.n; i += gridDim.x * CTA_THREADS) {
+    int2 stack[STACK_DEPTH];
+    for (uint32_t base = blockIdx.x * CTA_THREADS; base < A.n; base += gridDim.x * CTA_THREADS) {
+        const uint32_t i = base + threadIdx.x;
+        const bool alive = i < A.n;
         Ray ray;
-        ray.o = v3(A.origins[3 * i], A.origins[3 * i + 1], A.origins[3 * i + 2]);
-        ray.d = om::unit(v3(A.dirs[3 * i], A.dirs[3 * i + 1], A.dirs[3 * i + 2]));
-        Hit h = closest_hit<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, cn);
+        ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
+        if (alive) {
+            ray.o = v3(A.origins[3 * i], A.origins[3 * i + 1], A.origins[3 * i + 2]);
+            ray.d = om::unit(v3(A.dirs[3 * i], A.dirs[3 * i + 1], A.dirs[3 * i + 2]));
+        }
+        Hit h = closest_hit_warp<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
+        if (!alive) continue;
         const bool hit = h.ref != omd::REF_NONE;
         if (hit) finish_hit(sv, A.scene, ray, A.tmin, h);
         if (A.ids) A.ids[i] = hit ? (((unsigned long long)(omd::ref_type(h.ref) + 1u) << 32) | (unsigned long long)(omd::ref_index(h.ref) + 1u)) : 0ull;
