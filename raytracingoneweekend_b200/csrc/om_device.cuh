@@ -45,9 +45,10 @@ struct Rng {
     uint32_t k0, k1, a, b, draw;
     uint32_t b0, b1, b2, b3;
 };
-// Out of line on purpose: ~90 instructions that every draw site would otherwise inline (the first
-// kernels were > 100 KB of SASS and stalled on instruction fetch).  Values travel in registers.
-__device__ __noinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
+// Inlined at a handful of draw sites that the warp reaches CONVERGED (see rng_take): the first
+// kernels called an out-of-line copy from every scalar draw, lane by lane, and spent 12 % of all
+// issued instructions there at 3.7 active lanes.
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
     uint32_t c3 = 0u;  // STREAM_PATH
 #pragma unroll
     for (int r = 0; r < 10; r++) {
@@ -58,32 +59,47 @@ __device__ __noinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c
     }
     return make_uint4(c0, c1, c2, c3);
 }
-__device__ __forceinline__ void philox_block(Rng& g) {
-    const uint4 b = philox4x32_10(g.draw >> 2, g.a, g.b, g.k0, g.k1);
-    g.b0 = b.x; g.b1 = b.y; g.b2 = b.z; g.b3 = b.w;
-}
 __device__ __forceinline__ void rng_init(Rng& g, uint32_t k0, uint32_t k1, uint32_t pixel, uint32_t sample) {
     g.k0 = k0; g.k1 = k1; g.a = pixel; g.b = sample; g.draw = 0;
 }
-__device__ __forceinline__ float rng_f32(Rng& g) {  // utils.rs:25: uniform [0,1), 24 bits
-    const uint32_t lane = g.draw & 3u;
-    if (lane == 0u) philox_block(g);
-    g.draw++;
-    const uint32_t u = lane == 0u ? g.b0 : (lane == 1u ? g.b1 : (lane == 2u ? g.b2 : g.b3));
-    return (float)(u >> 8) * 5.9604644775390625e-8f;
+__device__ __forceinline__ float u32_to_f32(uint32_t u) { return (float)(u >> 8) * 5.9604644775390625e-8f; }  // utils.rs:25: uniform [0,1), 24 bits
+__device__ __forceinline__ uint32_t sel4(uint32_t i, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    return i == 0u ? a : (i == 1u ? b : (i == 2u ? c : d));
 }
-__device__ __forceinline__ float rng_range(Rng& g, float mn, float mx) { return rng_f32(g) * (mx - mn) + mn; }  // utils.rs:26
+// The next N (<= 4) draws of the stream, i.e. words draw .. draw+N-1 of the Philox block sequence
+// (word i lives in block i/4), with at most ONE block computation that every calling lane performs
+// together: the cached block serves the words before the next block boundary, the new block the
+// rest.  Same values in the same order as N calls of the oracle's next_f32().
+template <int N>
+__device__ __forceinline__ void rng_take(Rng& g, float* out) {
+    const uint32_t pos = g.draw & 3u;
+    const bool need = pos == 0u || pos + (uint32_t)N > 4u;
+    uint4 nb = make_uint4(g.b0, g.b1, g.b2, g.b3);
+    if (need) nb = philox4x32_10((g.draw + (uint32_t)N - 1u) >> 2, g.a, g.b, g.k0, g.k1);
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        const uint32_t j = pos + (uint32_t)i;
+        const uint32_t w = (pos != 0u && j < 4u) ? sel4(j, g.b0, g.b1, g.b2, g.b3) : sel4(j & 3u, nb.x, nb.y, nb.z, nb.w);
+        out[i] = u32_to_f32(w);
+    }
+    g.b0 = nb.x; g.b1 = nb.y; g.b2 = nb.z; g.b3 = nb.w;
+    g.draw += (uint32_t)N;
+}
+__device__ __forceinline__ float rng_f32(Rng& g) { float v; rng_take<1>(g, &v); return v; }
+__device__ __forceinline__ float to_range(float u, float mn, float mx) { return u * (mx - mn) + mn; }  // utils.rs:26
 __device__ __forceinline__ V3 rand_in_unit_sphere(Rng& g) {  // vec3.rs:92-97
     for (;;) {
-        const float x = rng_range(g, -1.f, 1.f), y = rng_range(g, -1.f, 1.f), z = rng_range(g, -1.f, 1.f);
-        const V3 p = v3(x, y, z);
+        float u[3];
+        rng_take<3>(g, u);
+        const V3 p = v3(to_range(u[0], -1.f, 1.f), to_range(u[1], -1.f, 1.f), to_range(u[2], -1.f, 1.f));
         if (om::length_squared(p) < 1.f) return p;
     }
 }
 __device__ __forceinline__ V3 rand_in_unit_disc(Rng& g) {  // vec3.rs:108-113
     for (;;) {
-        const float x = rng_range(g, -1.f, 1.f), y = rng_range(g, -1.f, 1.f);
-        const V3 p = v3(x, y, 0.f);
+        float u[2];
+        rng_take<2>(g, u);
+        const V3 p = v3(to_range(u[0], -1.f, 1.f), to_range(u[1], -1.f, 1.f), 0.f);
         if (om::length_squared(p) < 1.f) return p;
     }
 }
@@ -654,8 +670,10 @@ __device__ __forceinline__ Ray camera_ray(const om_camera& c, float u, float v, 
 __device__ __forceinline__ Ray primary_ray(const RenderArgs& A, uint32_t pxl, uint32_t sample, Rng& g) {
     const uint32_t line = pxl / A.width, col = pxl - A.width * line;
     const uint32_t code = A.jitter[sample];
-    const float i_rand = (rng_f32(g) + (float)((code >> 1) & 1u)) / 2.f;
-    const float j_rand = (rng_f32(g) + (float)(code & 1u)) / 2.f;
+    float jr[2];
+    rng_take<2>(g, jr);
+    const float i_rand = (jr[0] + (float)((code >> 1) & 1u)) / 2.f;
+    const float j_rand = (jr[1] + (float)(code & 1u)) / 2.f;
     const float u = ((float)col + i_rand) / ((float)A.width - 1.f);
     const float v = 1.0f - ((float)line + j_rand) / ((float)A.height - 1.f);
     const V3 disc = rand_in_unit_disc(g);
