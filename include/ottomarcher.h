@@ -163,8 +163,11 @@ enum {
     OM_RENDER_FAST_MATH = 1u << 1,
     /* closest hit by linear scan in the reference's list order (hits.rs:270-286), no BVH.     */
     OM_RENDER_BRUTE_FORCE = 1u << 2,
-    /* wavefront pipeline (raygen / intersect / shade / compact kernels) instead of the
-     * persistent path-regeneration kernel.                                                    */
+    /* wavefront pipeline instead of the persistent path-regeneration kernel: per bounce an extend
+     * kernel (BVH traversal, rays refilled from a queue), a shade kernel (sky / scatter by material
+     * class, Stats::add, next sample or pixel; also advances the marched rays a bounded number of
+     * steps) and a ballot+popc live-ray compaction; the last few thousand paths are finished by the
+     * persistent kernel.  Same results bit for bit.  om_render_launch blocks until the tail starts. */
     OM_RENDER_WAVEFRONT = 1u << 3,
     /* keep primitives and BVH in global memory even if they fit in shared memory.             */
     OM_RENDER_NO_SMEM_SCENE = 1u << 4,

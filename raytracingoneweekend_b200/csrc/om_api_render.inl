@@ -136,6 +136,13 @@ struct om_render {
     bool use_smem = false;
     size_t smem_bytes = 0;
     int grid = 0;
+    // wavefront pipeline (OM_RENDER_WAVEFRONT)
+    omk::WfArgs wf;               // device arrays; n_slots == 0: not allocated
+    int wf_grid_extend = 0, wf_grid_small = 0;
+    bool wf_smem = false;
+    uint32_t* wf_host_ctr = nullptr;  // pinned: wf::G_WORDS words per in-flight batch (2 batches)
+    cudaEvent_t wf_ev[2] = {nullptr, nullptr};
+    uint32_t n_uniform = 0;       // samples every live pixel has after the launches so far
 };
 
 namespace {
@@ -208,6 +215,12 @@ om_status om_render_destroy(om_render* r) {
     for (EventPair& e : r->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (EventPair& e : r->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     cudaFree(r->acc); cudaFree(r->aux); cudaFree(r->jitter); cudaFree(r->counters); cudaFree(r->live_list); cudaFree(r->live_count); cudaFree(r->staging);
+    if (r->wf.n_slots) {
+        cudaFree(r->wf.s_ray); cudaFree(r->wf.s_st); cudaFree(r->wf.s_live);
+        cudaFree(r->wf.q_ray[0]); cudaFree(r->wf.q_ray[1]); cudaFree(r->wf.q_march[0]); cudaFree(r->wf.q_march[1]); cudaFree(r->wf.q_shade[0]); cudaFree(r->wf.q_shade[1]); cudaFree(r->wf.ctr);
+    }
+    if (r->wf_host_ctr) cudaFreeHost(r->wf_host_ctr);
+    for (int i = 0; i < 2; i++) if (r->wf_ev[i]) cudaEventDestroy(r->wf_ev[i]);
     if (r->own_stream) cudaStreamDestroy(r->own_stream);
     cudaSetDevice(prev);
     delete r;
@@ -226,7 +239,6 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
     if (p.part_world > 1 && p.part_rank >= p.part_world) return fail(OM_ERR_INVALID, "om_render_create: part_rank >= part_world");
     if ((p.flags & OM_RENDER_ADAPTIVE) && (p.sample_base != 0 || (p.sample_count != 0 && p.sample_count != p.spp_max)))
         return fail(OM_ERR_INVALID, "om_render_create: adaptive retirement needs all of a pixel's samples in order; use the chunk partition, not an spp slice");
-    if (p.flags & OM_RENDER_WAVEFRONT) return fail(OM_ERR_UNSUPPORTED, "om_render_create: the wavefront pipeline is not built yet");
     int dev = 0;
     om_status st = pick_device(p.device, dev);
     if (st != OM_OK) return st;
@@ -236,6 +248,7 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
     r->cam = *cam;
     r->p = p;
     r->dev = dev;
+    memset(&r->wf, 0, sizeof r->wf);
     r->npx = p.width * p.height;
     r->budget = p.sample_count ? p.sample_count : (p.spp_max - p.sample_base);
 #define OM_TRY(call)                                 \
@@ -277,6 +290,25 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             return fail(OM_ERR_CUDA, "render kernel cannot be resident on device %d (%s)", dev, cudaGetErrorString(e));
         }
         r->grid = occ * r->props.sms;
+        if (p.flags & OM_RENDER_WAVEFRONT) {
+            // slot pool: resident in L2 (72 B of path state per slot), never more slots than pixels
+            uint32_t want = 1u << 20;
+            if (const char* e = getenv("OM_WF_SLOTS")) { const long v = atol(e); if (v >= 1024 && v <= (1l << 24)) want = (uint32_t)v; }  // tuning knob
+            const uint32_t n_slots = std::min<uint32_t>(want, (r->npx + 31u) & ~31u);
+            omk::WfArgs& w = r->wf;
+            CU(cudaMalloc(&w.s_ray, size_t(n_slots) * 32)); CU(cudaMalloc(&w.s_st, size_t(n_slots) * 64)); CU(cudaMalloc(&w.s_live, (size_t(n_slots) + 511u) & ~size_t(511)));
+            CU(cudaMalloc(&w.q_ray[0], size_t(n_slots) * 4)); CU(cudaMalloc(&w.q_ray[1], size_t(n_slots) * 4)); CU(cudaMalloc(&w.q_march[0], size_t(n_slots) * 4)); CU(cudaMalloc(&w.q_march[1], size_t(n_slots) * 4));
+            for (int i = 0; i < 2; i++) CU(cudaMalloc(&w.q_shade[i], size_t(n_slots) * 4 * omk::wf::N_CLS));
+            CU(cudaMalloc(&w.ctr, omk::wf::G_WORDS * 4));
+            w.n_slots = n_slots;
+            CU(cudaMallocHost(&r->wf_host_ctr, 2 * omk::wf::G_WORDS * 4));
+            for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&r->wf_ev[i], cudaEventDisableTiming));
+            r->wf_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + om_exact::wf_stage_bytes() + 1024u <= r->props.smem_optin / 2;
+            int o2 = exact ? om_exact::wf_extend_occupancy(r->wf_smem, count, r->wf_smem ? hot_bytes : 0) : om_fast::wf_extend_occupancy(r->wf_smem, count, r->wf_smem ? hot_bytes : 0);
+            if (o2 < 1) return fail(OM_ERR_CUDA, "wavefront extend kernel cannot be resident on device %d", dev);
+            r->wf_grid_extend = o2 * r->props.sms;
+            r->wf_grid_small = 8 * r->props.sms;
+        }
         return OM_OK;
     };
     OM_TRY(body());
@@ -302,8 +334,66 @@ om_status om_render_reset(om_render* r) {
     CU(cudaMemsetAsync(r->aux, 0, size_t(r->npx) * sizeof(uint4), r->stream));
     CU(cudaMemsetAsync(r->counters, 0, omk::ctr::CTR_COUNT * sizeof(unsigned long long), r->stream));
     r->have_live = false;
+    r->n_uniform = 0;
     return OM_OK;
 }
+
+namespace {
+// The wavefront loop: iterations are launched in batches; after each batch the counters are copied to
+// pinned memory and the host decides, one batch behind the GPU, whether live rays remain.  When few
+// are left the persistent kernel finishes the pixels (it restarts their unfinished sample from the
+// Philox counters, so nothing is lost or counted twice).
+om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
+    const bool exact = (r->p.flags & OM_RENDER_FAST_MATH) == 0, count = (r->p.flags & OM_RENDER_COUNTERS) != 0;
+    omk::WfArgs w = r->wf;
+    w.n_target = n_target;
+    const size_t smem = r->wf_smem ? r->smem_bytes : 0;
+    CU(cudaMemsetAsync(w.ctr, 0, omk::wf::G_WORDS * 4, r->stream));
+    CU(cudaMemsetAsync(w.s_live, 0, (size_t(w.n_slots) + 511u) & ~size_t(511), r->stream));
+    w.it = 0; w.init = 1;
+    cudaError_t e = exact ? om_exact::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream) : om_fast::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream);
+    if (e == cudaSuccess) e = om_exact::launch_wf_compact(w, r->wf_grid_small, r->stream);
+    if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_wf_shade(init) launch failed: %s", cudaGetErrorString(e));
+    w.init = 0;
+    const uint32_t BATCH = 16, TAIL = 24576;
+    uint32_t it = 0;
+    bool pending[2] = {false, false};
+    uint32_t it_at[2] = {0, 0};
+    for (uint32_t batch = 0;; batch++) {
+        const int slot = batch & 1;
+        if (pending[slot]) {  // result of batch - 2
+            CU(cudaEventSynchronize(r->wf_ev[slot]));
+            pending[slot] = false;
+            const uint32_t* h = r->wf_host_ctr + slot * omk::wf::G_WORDS;
+            const uint32_t* hs = h + (it_at[slot] % 3u) * omk::wf::C_SET_WORDS;
+            uint32_t live = hs[omk::wf::C_N_RAY] + hs[omk::wf::C_N_MARCH];
+            for (int c = 0; c < omk::wf::N_CLS; c++) live += hs[omk::wf::C_N_SHADE + omk::wf::C_STRIDE * c];
+            if (live < TAIL) break;
+        }
+        for (uint32_t k = 0; k < BATCH; k++, it++) {
+            w.it = it;
+            e = exact ? om_exact::launch_wf_extend(a, w, r->wf_smem, count, r->wf_grid_extend, smem, r->stream)
+                      : om_fast::launch_wf_extend(a, w, r->wf_smem, count, r->wf_grid_extend, smem, r->stream);
+            if (e == cudaSuccess) e = exact ? om_exact::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream) : om_fast::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream);
+            if (e == cudaSuccess) e = om_exact::launch_wf_compact(w, r->wf_grid_small, r->stream);
+            if (e != cudaSuccess) return fail(OM_ERR_CUDA, "wavefront launch failed: %s", cudaGetErrorString(e));
+        }
+        // snapshot: the rays of iteration `it` are counted in set it % 3
+        uint32_t* h = r->wf_host_ctr + slot * omk::wf::G_WORDS;
+        CU(cudaMemcpyAsync(h, w.ctr, omk::wf::G_WORDS * 4, cudaMemcpyDeviceToHost, r->stream));
+        it_at[slot] = it;
+        CU(cudaEventRecord(r->wf_ev[slot], r->stream));
+        pending[slot] = true;
+    }
+    for (int i = 0; i < 2; i++)
+        if (pending[i]) { CU(cudaEventSynchronize(r->wf_ev[i])); }
+    // tail: the persistent kernel brings every pixel to the target
+    a.n_target = n_target;
+    e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream) : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+    if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_render (tail) launch failed: %s", cudaGetErrorString(e));
+    return OM_OK;
+}
+}  // namespace
 
 om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     if (!r) return fail(OM_ERR_INVALID, "om_render_launch: NULL handle");
@@ -318,9 +408,16 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     CU(cudaMemsetAsync(r->counters + omk::ctr::CTR_TICKET, 0, sizeof(unsigned long long), r->stream));
     CU(cudaEventRecord(ev.a, r->stream));
     const bool exact = (r->p.flags & OM_RENDER_FAST_MATH) == 0, count = (r->p.flags & OM_RENDER_COUNTERS) != 0;
-    cudaError_t e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
-                          : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
-    if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
+    const uint32_t n_target = (uint32_t)std::min<uint64_t>(r->budget, uint64_t(r->n_uniform) + a.spp_pass);
+    if (r->p.flags & OM_RENDER_WAVEFRONT) {
+        om_status s = run_wavefront(r, a, n_target);
+        if (s != OM_OK) { r->pool.push_back(ev); return s; }
+    } else {
+        cudaError_t e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
+                              : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+        if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
+    }
+    r->n_uniform = n_target;
     if (adaptive) {  // next pass walks only the pixels that still want samples
         CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
         k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, r->live_list, r->live_count);

@@ -24,6 +24,7 @@ struct RenderArgs {
     uint32_t width, height, npx;
     uint32_t spp_budget;   // samples this handle owns per pixel
     uint32_t spp_pass;     // at most this many more samples per pixel in this launch
+    uint32_t n_target;     // if non-zero: bring every live pixel to min(spp_budget, n_target) samples instead (wavefront tail)
     uint32_t sample_base;  // global index of the handle's first sample (spp-slice partition)
     uint32_t max_depth;
     float tmin, tmax;
@@ -38,6 +39,34 @@ struct RenderArgs {
     unsigned long long* counters;
     const uint32_t* live_list;  // adaptive mode: compacted list of live pixels, or nullptr
     const uint32_t* live_count;
+};
+
+// Wavefront pipeline (om_wavefront.cuh).  A SLOT carries one path; it is bound to one pixel until
+// that pixel has all the samples of this launch, then takes the next unstarted pixel.
+namespace wf {
+// per-iteration counter set (three sets rotate: iteration i uses set i % 3, pushes the next
+// iteration's rays into set (i+1) % 3 and clears set (i+2) % 3)
+// every counter sits on its own 128-byte line: same-line atomics serialise in one L2 slice
+enum { C_STRIDE = 32, C_N_RAY = 0, C_N_MARCH = 1 * C_STRIDE, C_CUR_RAY = 2 * C_STRIDE, C_N_SHADE = 3 * C_STRIDE /* + C_STRIDE * class */, C_SET_WORDS = 8 * C_STRIDE };
+// shade classes: what a finished segment needs next (a warp of k_wf_shade only ever sees one class)
+enum { CLS_SKY = 0, CLS_LAMBERTIAN = 1, CLS_METAL = 2, CLS_DIELECTRIC = 3, CLS_OTHER = 4 /* hit on anything but a Sphere */, N_CLS = 5 };
+// global words after the three sets
+enum { G_NEXT_WORK = 3 * C_SET_WORDS, G_WORDS = 3 * C_SET_WORDS + C_STRIDE };
+}  // namespace wf
+struct WfArgs {
+    uint32_t n_slots;
+    uint32_t it;          // iteration index
+    uint32_t n_target;    // every live pixel is brought to min(spp_budget, n_target) samples
+    uint32_t init;        // shade kernel: 1 = first launch (every slot takes a pixel; nothing to shade)
+    float4* s_ray;        // 2 per slot: {origin.xyz, sample index (uint bits)}, {direction.xyz (unit), pixel (uint bits, 0xFFFFFFFF = free)}
+    float4* s_st;         // 4 per slot: {throughput.rgb, primary-hit t}, {segment, Philox draw, bloom lo, hi},
+                          //             {hit t, hit ref, march t, march iterations left (0xFFFFFFFF: unstuck first)}, unused
+    uint8_t* s_live;      // 1 = the slot has a ray for the next iteration (set by k_wf_shade, gathered and cleared by k_wf_compact)
+    uint32_t* q_ray[2];   // slots with a ray to extend (ping-pong)
+    uint32_t* q_march[2]; // slots whose ray enters the marched objects' bounds before its traced hit (ping-pong: marches span iterations)
+    uint32_t* q_shade[2]; // each: wf::N_CLS queues of n_slots entries: slots whose segment is resolved, by shade class (ping-pong:
+                          // a march that ends during iteration i queues its slot for the shading of iteration i + 1)
+    uint32_t* ctr;        // wf::G_WORDS words
 };
 
 struct TraceArgs {

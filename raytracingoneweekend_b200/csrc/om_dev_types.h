@@ -5,7 +5,7 @@
 //  hot image  (staged into shared memory by TMA bulk copy when it fits; else read from global/L2)
 //      BVH nodes 64 B | sphere world->local rows 48 B | cube world->local rows 48 B |
 //      triangle 64 B | infinite plane 32 B | parallelogram 64 B | always-test refs 4 B |
-//      marched sphere 16 B | marched box 32 B | marched torus 144 B
+//      marched sphere 16 B | marched box 32 B | marched torus 144 B | sphere material type 1 B
 //  cold image (global memory; touched once per hit, not per test)
 //      sphere local->world rows 48 B | cube local->world rows 48 B | material+bloom 32 B per object
 #pragma once
@@ -47,7 +47,7 @@ struct SceneHeader {
     // object and cannot start inside one.  lo > hi when the scene has no marched object.
     float march_lo[3], march_hi[3];
     uint32_t n_marched;
-    uint32_t pad;
+    uint32_t off_sph_mat;  // hot image: one byte per sphere = its material type (shade class of a hit, om_wavefront.cuh)
 };
 
 }  // namespace omd

@@ -118,6 +118,10 @@ struct SceneView {
         return __ldg(hot_g + u);
     }
     __device__ __forceinline__ float4 cold(uint32_t u) const { return __ldg(cold_g + u); }
+    __device__ __forceinline__ uint32_t hot_byte(uint32_t u, uint32_t i) const {  // byte i of the section starting at unit u
+        if (SMEM) return reinterpret_cast<const uint8_t*>(om_smem + u)[i];
+        return __ldg(reinterpret_cast<const uint8_t*>(hot_g + u) + i);
+    }
 };
 
 struct Ray {
@@ -598,8 +602,10 @@ __device__ __forceinline__ void finish_hit(const SceneView<SMEM>& sv, const Scen
         const float div = om::dot(n, r.d);
         h.point = ray_at(r, h.t);
         h.normal = n * copysignf(1.f, -div);
+    } else {  // marched hit (hits.rs:322-328): the accepted point and the nearest object's normal there
+        h.point = ray_at(r, h.t);
+        h.normal = marched_normal(sv, S, h.ref, h.point);
     }
-    // marched hits: point/normal were set by march()
 }
 
 // ---- materials.rs --------------------------------------------------------------------------------
@@ -809,6 +815,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_render(const __grid_constant
             st.avg_depth = __uint_as_float(x.x); st.bad_avgs = x.y; st.bloom_lo = x.z; st.bloom_hi = x.w;
             st.color = stats_color_of(st.sum, st.n);
             todo = A.spp_budget > st.n ? min(A.spp_budget - st.n, A.spp_pass) : 0u;
+            if (A.n_target) { const uint32_t tg = min(A.spp_budget, A.n_target); todo = tg > st.n ? tg - st.n : 0u; }
             if (adaptive && st.bad_avgs >= 5u) todo = 0u;
         }
         const bool touched = todo > 0u;

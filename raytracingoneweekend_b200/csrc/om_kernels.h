@@ -6,6 +6,11 @@
     namespace NS {                                                                                                                 \
     int render_occupancy(bool smem, bool count, size_t smem_bytes);                                                                \
     cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st);      \
+    int wf_extend_occupancy(bool smem, bool count, size_t smem_bytes);                                                             \
+    cudaError_t launch_wf_extend(const omk::RenderArgs& a, const omk::WfArgs& w, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st); \
+    size_t wf_stage_bytes();                                                                                                       \
+    cudaError_t launch_wf_compact(const omk::WfArgs& w, int grid, cudaStream_t st);                                              \
+    cudaError_t launch_wf_shade(const omk::RenderArgs& a, const omk::WfArgs& w, bool count, int grid, cudaStream_t st);          \
     cudaError_t launch_primary(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st, uint32_t mode,   \
                                uint32_t sample_index, unsigned long long* ids, float* t);                                         \
     cudaError_t launch_trace(const omk::TraceArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st);                    \

@@ -3,4 +3,7 @@
 #define OM_EXACT 1
 #define OM_NS om_exact
 #include "om_device.cuh"
+namespace OM_NS {
+#include "om_wavefront.cuh"
+}
 #include "om_launch.inl"

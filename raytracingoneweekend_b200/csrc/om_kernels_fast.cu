@@ -2,4 +2,7 @@
 #define OM_EXACT 0
 #define OM_NS om_fast
 #include "om_device.cuh"
+namespace OM_NS {
+#include "om_wavefront.cuh"
+}
 #include "om_launch.inl"

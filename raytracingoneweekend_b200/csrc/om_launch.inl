@@ -44,4 +44,40 @@ cudaError_t launch_trace(const omk::TraceArgs& a, bool smem, int grid, size_t sm
     return cudaGetLastError();
 }
 
+// ---- wavefront pipeline (om_wavefront.cuh) ----
+size_t wf_stage_bytes() { return WF_STAGE_BYTES; }
+int wf_extend_occupancy(bool smem, bool count, size_t scene_bytes) {
+    int n = 0;
+    cudaError_t e;
+    const size_t total = (smem ? scene_bytes : 0) + WF_STAGE_BYTES;
+    if (smem) {
+        if (count) { prep(k_wf_extend<true, true>, total); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<true, true>, WF_EXT_THREADS, total); }
+        else { prep(k_wf_extend<true, false>, total); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<true, false>, WF_EXT_THREADS, total); }
+    } else {
+        if (count) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<false, true>, WF_EXT_THREADS, total);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<false, false>, WF_EXT_THREADS, total);
+    }
+    return e == cudaSuccess ? n : 0;
+}
+cudaError_t launch_wf_extend(const omk::RenderArgs& a, const omk::WfArgs& w, bool smem, bool count, int grid, size_t scene_bytes, cudaStream_t st) {
+    const size_t total = (smem ? scene_bytes : 0) + WF_STAGE_BYTES;
+    if (smem) {
+        if (count) k_wf_extend<true, true><<<grid, WF_EXT_THREADS, total, st>>>(a, w);
+        else k_wf_extend<true, false><<<grid, WF_EXT_THREADS, total, st>>>(a, w);
+    } else {
+        if (count) k_wf_extend<false, true><<<grid, WF_EXT_THREADS, total, st>>>(a, w);
+        else k_wf_extend<false, false><<<grid, WF_EXT_THREADS, total, st>>>(a, w);
+    }
+    return cudaGetLastError();
+}
+cudaError_t launch_wf_shade(const omk::RenderArgs& a, const omk::WfArgs& w, bool count, int grid, cudaStream_t st) {
+    if (count) k_wf_shade<true><<<grid, WF_THREADS, 0, st>>>(a, w);
+    else k_wf_shade<false><<<grid, WF_THREADS, 0, st>>>(a, w);
+    return cudaGetLastError();
+}
+cudaError_t launch_wf_compact(const omk::WfArgs& w, int grid, cudaStream_t st) {
+    k_wf_compact<<<grid, WF_THREADS, 0, st>>>(w);
+    return cudaGetLastError();
+}
+
 }  // namespace OM_NS

@@ -248,6 +248,12 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
         }
         grow(lo, hi);
     }
+    h.off_sph_mat = hot.units();
+    for (size_t i = 0; i < L.spheres.size(); i += 16) {
+        uint32_t w[4] = {0, 0, 0, 0};
+        for (size_t k = 0; k < 16 && i + k < L.spheres.size(); k++) w[k >> 2] |= (L.spheres[i + k].material.mat_type & 0xFFu) << (8 * (k & 3));
+        hot.u4(w[0], w[1], w[2], w[3]);
+    }
     h.n_marched = h.n[PT_MSPHERE] + h.n[PT_MBOX] + h.n[PT_MTORUS];
     for (int a = 0; a < 3; a++) {
         if (h.n_marched == 0) { h.march_lo[a] = kInf; h.march_hi[a] = -kInf; }

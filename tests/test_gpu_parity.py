@@ -258,3 +258,61 @@ def test_golden_fixtures(api, A, rtiow):
     rel = np.abs(t[tr] - gp["t_center"][tr]) / gp["t_center"][tr]
     assert np.median(rel) <= 1e-5 and rel.max() <= 5e-3
     r.close()
+
+
+# ---- wavefront pipeline (OM_RENDER_WAVEFRONT): same bits as the oracle and as the persistent kernel ----
+@pytest.mark.parametrize("W,H,spp,depth,flags_extra", [(64, 48, 6, 50, 0), (37, 23, 5, 50, 0), (2, 2, 3, 50, 0), (48, 32, 4, 1, 0), (40, 30, 3, 3, 0),
+                                                       (64, 48, 6, 50, 4), (64, 48, 6, 50, 16)])  # 4 = brute force, 16 = scene in global memory
+def test_wavefront_bit_exact_fixed_spp(api, A, rtiow, W, H, spp, depth, flags_extra):
+    fz, osc = rtiow
+    cam = cam_rtiow(api, W / H)
+    p = api.render_params(W, H, spp, max_depth=depth, seed=21, flags=A.RENDER_WAVEFRONT | flags_extra)
+    r = api.Renderer(fz, cam, p)
+    r.launch(0); r.sync()
+    g = r.read_pixels()
+    ref = osc.render(cam, api.render_params(W, H, spp, max_depth=depth, seed=21, flags=0))
+    assert_pixels_equal(g, ref["pixels"])
+    assert r.samples_done() == ref["credited"] == W * H * spp and r.samples_traced() == ref["traced"]
+    r.close()
+
+
+def test_wavefront_bit_exact_adaptive_multipass_and_marched(api, A, rtiow, mixed, O):
+    fz, osc = rtiow
+    cam = cam_rtiow(api, 1.5)
+    p = api.render_params(60, 40, 40, seed=4, flags=A.RENDER_ADAPTIVE | A.RENDER_WAVEFRONT)
+    r = api.Renderer(fz, cam, p)
+    for _ in range(5):
+        r.launch(8)
+    r.sync()
+    ref = osc.render(cam, api.render_params(60, 40, 40, seed=4, flags=A.RENDER_ADAPTIVE))
+    assert_pixels_equal(r.read_pixels(), ref["pixels"])
+    assert r.samples_done() == ref["credited"] and r.samples_traced() == ref["traced"]
+    r.close()
+    fzx, oscx = mixed
+    camx = api.Camera.new((6, 3, 7), (0, 0.5, 0), (0, 1, 0), 40.0, 1.5, 0.05, 9.0)
+    p = api.render_params(48, 32, 4, seed=2, flags=A.RENDER_WAVEFRONT)
+    r = api.Renderer(fzx, camx, p); r.launch(0); r.sync()
+    assert_pixels_equal(r.read_pixels(), oscx.render(camx, api.render_params(48, 32, 4, seed=2))["pixels"])
+    r.close()
+    fzm = api.FrozenHittableList.generate("marched", 3)
+    oscm = oracle_scene_from(O, fzm)
+    p = api.render_params(32, 24, 2, seed=2, flags=A.RENDER_WAVEFRONT)
+    r = api.Renderer(fzm, cam_rtiow(api, 4 / 3), p); r.launch(0); r.sync()
+    assert_pixels_equal(r.read_pixels(), oscm.render(cam_rtiow(api, 4 / 3), api.render_params(32, 24, 2, seed=2))["pixels"])
+    r.close()
+
+
+@pytest.mark.parametrize("kind,seed", [("random_scene", 1), ("glass_heavy", 4), ("marched", 3)])
+def test_wavefront_equals_persistent_kernel_large(api, A, kind, seed):
+    """At a size the oracle cannot reach in seconds (more pixels than slots are exercised by the
+    pixel hand-over and the tail): both device paths must agree bit for bit."""
+    fz = api.FrozenHittableList.generate(kind, seed)
+    cam = cam_rtiow(api, 16 / 9)
+    out = []
+    for fl in (0, A.RENDER_WAVEFRONT):
+        r = api.Renderer(fz, cam, api.render_params(640, 360, 6, seed=9, flags=fl))
+        r.launch(4); r.launch(0); r.sync()
+        out.append((r.read_pixels(), r.samples_done(), r.samples_traced()))
+        r.close()
+    assert_pixels_equal(out[0][0], out[1][0])
+    assert out[0][1:] == out[1][1:]
