@@ -175,6 +175,8 @@ def run_ours(args):
     fz = api.FrozenHittableList.generate(kind, seed, n_param)
     cam = make_camera(api, aspect)
     kw = dict(max_depth=MAX_DEPTH, tmin=TMIN, tmax=TMAX, seed=1)
+    if args.wavefront:
+        kw["flags"] = A.RENDER_WAVEFRONT
     dr = D.DistributedRenderer(fz, cam, W, H, spp, rank, world, mode="spp", device=local, **kw)
     stream = torch.cuda.Stream(device=local)  # a real stream: pointer 0 would mean "the handle's own"
     torch.cuda.set_stream(stream)              # NCCL collectives and the events below use it too
@@ -256,7 +258,8 @@ def run_ours(args):
     line = None
     if rank == 0:
         # ---- roofline of the dominant kernel (k_render): executed work x SURVEY §8(d) constants ----
-        pc = api.render_params(W, H, 16, flags=A.RENDER_COUNTERS, device=local, **kw)
+        kwc = dict(kw); kwc["flags"] = kw.get("flags", 0) | A.RENDER_COUNTERS
+        pc = api.render_params(W, H, 16, device=local, **kwc)
         rc = api.Renderer(fz, cam, pc)
         rc.launch(0)
         rc.sync()
@@ -269,7 +272,7 @@ def run_ours(args):
         achieved_tf = fps * samples_launch / (launch_ms * 1e-3) / 1e12
         roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf, "traffic": None,
                     "peak_source": "FMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
-                    "flops_per_sample": fps, "kernel": "k_render", "launch_ms": launch_ms,
+                    "flops_per_sample": fps, "kernel": "k_wf_extend + k_wf_shade + k_wf_compact (+ k_render tail)" if args.wavefront else "k_render", "launch_ms": launch_ms,
                     "per_sample": {k: c[k] / c["traced"] for k in ("segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals")},
                     "accumulate_hbm": {"bytes_per_launch": 64 * W * H, "note": "32 B read + 32 B write per pixel per launch"}}
         cpu = None
@@ -281,7 +284,7 @@ def run_ours(args):
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "%s: %s %dx%d, %d spp, depth %d, fixed spp" % (args.workload, kind, W, H, spp, MAX_DEPTH),
-                       "partition": "spp slices + 1 NCCL reduce" if world > 1 else "single GPU",
+                       "partition": "spp slices + 1 NCCL reduce" if world > 1 else "single GPU", "pipeline": "wavefront" if args.wavefront else "persistent kernel",
                        "l2": "scene is 93 KB in shared memory; per-step traffic is the 66 MB framebuffer, rewritten by reset() every step"},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 40},
             "gpu_launches": args.steps * (1 + (3 if world > 1 else 0)),
@@ -306,6 +309,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (a smaller number is NOT the headline config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--wavefront", action="store_true", help="use the wavefront pipeline (OM_RENDER_WAVEFRONT) instead of the persistent kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

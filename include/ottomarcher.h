@@ -173,7 +173,12 @@ enum {
     OM_RENDER_NO_SMEM_SCENE = 1u << 4,
     /* instrumented kernels: count segments, BVH node visits, primitive tests, SDF evaluations
      * (the executed-work figures of the FP32 roofline accounting); slower.                    */
-    OM_RENDER_COUNTERS = 1u << 5
+    OM_RENDER_COUNTERS = 1u << 5,
+    /* force the persistent path-regeneration kernel.  With neither this nor OM_RENDER_WAVEFRONT the
+     * library picks: wavefront when the scene image does not fit in shared memory (the BVH is then
+     * walked through L2, which wants many more rays in flight) or when it has more than 8 marched
+     * objects (long SDF marches stall the persistent kernel's warps); persistent kernel otherwise. */
+    OM_RENDER_PERSISTENT = 1u << 6
 };
 
 typedef struct om_render_params {

@@ -25,6 +25,7 @@ RENDER_ADAPTIVE = 1 << 0
 RENDER_FAST_MATH = 1 << 1
 RENDER_BRUTE_FORCE = 1 << 2
 RENDER_WAVEFRONT = 1 << 3
+RENDER_PERSISTENT = 1 << 6
 RENDER_NO_SMEM_SCENE = 1 << 4
 RENDER_COUNTERS = 1 << 5
 

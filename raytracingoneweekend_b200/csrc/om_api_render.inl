@@ -247,6 +247,7 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
     r->scene = const_cast<om_scene*>(frozen);
     r->cam = *cam;
     r->p = p;
+    if ((p.flags & OM_RENDER_WAVEFRONT) && (p.flags & OM_RENDER_PERSISTENT)) { delete r; return fail(OM_ERR_INVALID, "om_render_create: OM_RENDER_WAVEFRONT and OM_RENDER_PERSISTENT exclude each other"); }
     r->dev = dev;
     memset(&r->wf, 0, sizeof r->wf);
     r->npx = p.width * p.height;
@@ -290,7 +291,11 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             return fail(OM_ERR_CUDA, "render kernel cannot be resident on device %d (%s)", dev, cudaGetErrorString(e));
         }
         r->grid = occ * r->props.sms;
-        if (p.flags & OM_RENDER_WAVEFRONT) {
+        if (!(p.flags & (OM_RENDER_WAVEFRONT | OM_RENDER_PERSISTENT))) {  // automatic choice (see OM_RENDER_PERSISTENT)
+            const bool fits = hot_bytes + om_exact::wf_stage_bytes() + 1024u <= r->props.smem_optin / 2;
+            if (!fits || r->scene->fz.hdr.n_marched > 8u) r->p.flags |= OM_RENDER_WAVEFRONT;
+        }
+        if (r->p.flags & OM_RENDER_WAVEFRONT) {
             // slot pool: resident in L2 (72 B of path state per slot), never more slots than pixels
             uint32_t want = 1u << 20;
             if (const char* e = getenv("OM_WF_SLOTS")) { const long v = atol(e); if (v >= 1024 && v <= (1l << 24)) want = (uint32_t)v; }  // tuning knob
@@ -356,6 +361,11 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_wf_shade(init) launch failed: %s", cudaGetErrorString(e));
     w.init = 0;
     const uint32_t BATCH = 16, TAIL = 24576;
+    // OM_WF_TIMING=1 (development): device time of each kernel of iterations 8..39, printed to stderr
+    const bool timing = getenv("OM_WF_TIMING") != nullptr;
+    const uint32_t TIMED = 32;
+    std::vector<cudaEvent_t> tev;
+    if (timing) { tev.resize(4 * TIMED); for (auto& ev : tev) CU(cudaEventCreate(&ev)); }
     uint32_t it = 0;
     bool pending[2] = {false, false};
     uint32_t it_at[2] = {0, 0};
@@ -372,10 +382,14 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
         }
         for (uint32_t k = 0; k < BATCH; k++, it++) {
             w.it = it;
+            if (timing && it >= 8 && it < 8 + TIMED) CU(cudaEventRecord(tev[4 * (it - 8)], r->stream));
             e = exact ? om_exact::launch_wf_extend(a, w, r->wf_smem, count, r->wf_grid_extend, smem, r->stream)
                       : om_fast::launch_wf_extend(a, w, r->wf_smem, count, r->wf_grid_extend, smem, r->stream);
+            if (timing && it >= 8 && it < 8 + TIMED) CU(cudaEventRecord(tev[4 * (it - 8) + 1], r->stream));
             if (e == cudaSuccess) e = exact ? om_exact::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream) : om_fast::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream);
+            if (timing && it >= 8 && it < 8 + TIMED) CU(cudaEventRecord(tev[4 * (it - 8) + 2], r->stream));
             if (e == cudaSuccess) e = om_exact::launch_wf_compact(w, r->wf_grid_small, r->stream);
+            if (timing && it >= 8 && it < 8 + TIMED) CU(cudaEventRecord(tev[4 * (it - 8) + 3], r->stream));
             if (e != cudaSuccess) return fail(OM_ERR_CUDA, "wavefront launch failed: %s", cudaGetErrorString(e));
         }
         // snapshot: the rays of iteration `it` are counted in set it % 3
@@ -387,6 +401,20 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     }
     for (int i = 0; i < 2; i++)
         if (pending[i]) { CU(cudaEventSynchronize(r->wf_ev[i])); }
+    if (timing && it >= 8 + TIMED) {
+        CU(cudaStreamSynchronize(r->stream));
+        float t_ext = 0, t_sh = 0, t_co = 0, t_gap = 0;
+        for (uint32_t i = 0; i < TIMED; i++) {
+            float x;
+            cudaEventElapsedTime(&x, tev[4 * i], tev[4 * i + 1]); t_ext += x;
+            cudaEventElapsedTime(&x, tev[4 * i + 1], tev[4 * i + 2]); t_sh += x;
+            cudaEventElapsedTime(&x, tev[4 * i + 2], tev[4 * i + 3]); t_co += x;
+            if (i + 1 < TIMED) { cudaEventElapsedTime(&x, tev[4 * i + 3], tev[4 * i + 4]); t_gap += x; }
+        }
+        fprintf(stderr, "[om wavefront] per iteration (us): extend %.1f  shade %.1f  compact %.1f  gap %.1f  (slots %u)\n", 1e3f * t_ext / TIMED, 1e3f * t_sh / TIMED,
+                1e3f * t_co / TIMED, 1e3f * t_gap / (TIMED - 1), w.n_slots);
+    }
+    for (auto& ev : tev) cudaEventDestroy(ev);
     // tail: the persistent kernel brings every pixel to the target
     a.n_target = n_target;
     e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream) : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);

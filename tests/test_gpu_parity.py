@@ -309,10 +309,16 @@ def test_wavefront_equals_persistent_kernel_large(api, A, kind, seed):
     fz = api.FrozenHittableList.generate(kind, seed)
     cam = cam_rtiow(api, 16 / 9)
     out = []
-    for fl in (0, A.RENDER_WAVEFRONT):
+    for fl in (A.RENDER_PERSISTENT, A.RENDER_WAVEFRONT):
         r = api.Renderer(fz, cam, api.render_params(640, 360, 6, seed=9, flags=fl))
         r.launch(4); r.launch(0); r.sync()
         out.append((r.read_pixels(), r.samples_done(), r.samples_traced()))
         r.close()
     assert_pixels_equal(out[0][0], out[1][0])
     assert out[0][1:] == out[1][1:]
+
+
+def test_pipeline_flags_exclusive(api, A, rtiow):
+    fz, _ = rtiow
+    with pytest.raises(Exception):
+        api.Renderer(fz, cam_rtiow(api), api.render_params(16, 16, 1, flags=A.RENDER_PERSISTENT | A.RENDER_WAVEFRONT))

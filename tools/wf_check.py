@@ -30,7 +30,7 @@ for kind, seed in (("random_scene", 1), ("marched", 3), ("basic_scene", 1)):
     fz = api.FrozenHittableList.generate(kind, seed)
     cam = bench.make_camera(api, 1.5)
     for label, fl, spp, passes in (("fixed", 0, 12, None), ("fixed 3 passes", 0, 12, [5, 5, 5]), ("adaptive", A.RENDER_ADAPTIVE, 48, None), ("adaptive passes", A.RENDER_ADAPTIVE, 48, [8] * 6)):
-        a = run(fz, cam, 300, 200, spp, fl, passes)
+        a = run(fz, cam, 300, 200, spp, fl | A.RENDER_PERSISTENT, passes)
         b = run(fz, cam, 300, 200, spp, fl | A.RENDER_WAVEFRONT, passes)
         ok = same(a[0], b[0]) and a[1] == b[1] and a[2] == b[2]
         allok &= ok
@@ -41,7 +41,7 @@ if "--time" in sys.argv:
         kind, seed, n_param, W, H, _, aspect = bench.WORKLOADS[wl]
         fz = api.FrozenHittableList.generate(kind, seed, n_param)
         cam = bench.make_camera(api, aspect)
-        for fl in (0, A.RENDER_WAVEFRONT):
+        for fl in (A.RENDER_PERSISTENT, A.RENDER_WAVEFRONT):
             r = api.Renderer(fz, cam, api.render_params(W, H, spp, seed=1, flags=fl))
             for i in range(2):
                 r.reset(); r.launch(0); r.sync(); ms, _ = r.elapsed_ms()
