@@ -9,7 +9,7 @@ import os
 from . import _abi as A
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libottomarcher_cuda.so")
+LIB_PATH = os.environ.get("OM_LIB_PATH") or os.path.join(HERE, "libottomarcher_cuda.so")  # OM_LIB_PATH: development builds
 
 _lib = None
 

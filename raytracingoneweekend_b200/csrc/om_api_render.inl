@@ -133,7 +133,8 @@ struct om_render {
     std::vector<EventPair> pending, pool;
     float acc_ms = 0.f;
     uint32_t launches = 0;
-    bool use_smem = false;
+    bool use_smem = false;       // k_render: scene image in shared memory (one 1024-thread CTA per SM)
+    bool use_smem_hook = false;  // parity-hook kernels (two 256-thread CTAs per SM)
     size_t smem_bytes = 0;
     int grid = 0;
     // wavefront pipeline (OM_RENDER_WAVEFRONT)
@@ -280,11 +281,12 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             CU(cudaMalloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t)));
             CU(cudaMalloc(&r->live_count, sizeof(uint32_t)));
         }
-        // launch shape: persistent grid, hot image in shared memory when two CTAs still fit per SM
+        // launch shape: persistent grid of one CTA per SM, hot image in shared memory when it fits
         const bool exact = (p.flags & OM_RENDER_FAST_MATH) == 0, count = (p.flags & OM_RENDER_COUNTERS) != 0;
         const size_t hot_bytes = size_t(r->scene->fz.hdr.hot_units) * 16u;
-        r->use_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= r->props.smem_optin / 2;
-        r->smem_bytes = r->use_smem ? hot_bytes : 0;
+        r->use_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 2048u <= r->props.smem_optin;
+        r->use_smem_hook = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= r->props.smem_optin / 2;
+        r->smem_bytes = hot_bytes;  // each launch wrapper uses it only when its kernel keeps the scene in shared memory
         int occ = exact ? om_exact::render_occupancy(r->use_smem, count, r->smem_bytes) : om_fast::render_occupancy(r->use_smem, count, r->smem_bytes);
         if (occ < 1) {
             cudaError_t e = cudaGetLastError();
@@ -531,8 +533,8 @@ om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_index, 
     float* d_t = (float*)(d_ids + n);
     omk::RenderArgs a = make_args(r);
     const int grid = std::min(ublocks(n), r->props.sms * 8);
-    cudaError_t e = !(r->p.flags & OM_RENDER_FAST_MATH) ? om_exact::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t)
-                                                   : om_fast::launch_primary(a, r->use_smem, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t);
+    cudaError_t e = !(r->p.flags & OM_RENDER_FAST_MATH) ? om_exact::launch_primary(a, r->use_smem_hook, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t)
+                                                   : om_fast::launch_primary(a, r->use_smem_hook, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t);
     if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_primary launch failed: %s", cudaGetErrorString(e));
     CU(cudaMemcpyAsync(ids, d_ids, n * 8u, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaMemcpyAsync(t, d_t, n * 4u, cudaMemcpyDeviceToHost, r->stream));

@@ -32,6 +32,11 @@ constexpr float kInf = __builtin_huge_valf();
 constexpr float HIT_SIZE = 0.001f;  // hits.rs:113
 constexpr int UNSTUCK_MAX_STEPS = 1 << 20;
 constexpr int CTA_THREADS = 256;
+#ifndef OM_RENDER_THREADS
+#define OM_RENDER_THREADS 1024  // one CTA per SM: one copy of the scene image, 32 warps (64 registers) to hide the
+#define OM_RENDER_MIN_CTAS 1    // instruction-cache misses of this 70 KB kernel: +23 % over 2 x 256 threads at 92 registers
+#endif
+constexpr int RENDER_THREADS = OM_RENDER_THREADS;  // k_render only
 
 using omk::RenderArgs;
 using omk::TraceArgs;
@@ -779,7 +784,7 @@ __device__ __forceinline__ void stage_scene_smem(const float4* hot_g, uint32_t u
 // coalesced read and write of the pixel's 32-byte state.
 // ============================================================================================
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(CTA_THREADS, 2) k_render(const __grid_constant__ RenderArgs A) {
+__global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(const __grid_constant__ RenderArgs A) {
     if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
     SceneView<SMEM> sv;
     sv.hot_g = A.hot_g;

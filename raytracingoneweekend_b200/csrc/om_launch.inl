@@ -11,22 +11,22 @@ int render_occupancy(bool smem, bool count, size_t smem_bytes) {
     int n = 0;
     cudaError_t e;
     if (smem) {
-        if (count) { prep(k_render<true, true>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, true>, CTA_THREADS, smem_bytes); }
-        else { prep(k_render<true, false>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, false>, CTA_THREADS, smem_bytes); }
+        if (count) { prep(k_render<true, true>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, true>, RENDER_THREADS, smem_bytes); }
+        else { prep(k_render<true, false>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, false>, RENDER_THREADS, smem_bytes); }
     } else {
-        if (count) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, true>, CTA_THREADS, 0);
-        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, false>, CTA_THREADS, 0);
+        if (count) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, true>, RENDER_THREADS, 0);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, false>, RENDER_THREADS, 0);
     }
     return e == cudaSuccess ? n : 0;
 }
 
 cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st) {
     if (smem) {
-        if (count) { prep(k_render<true, true>, smem_bytes); k_render<true, true><<<grid, CTA_THREADS, smem_bytes, st>>>(a); }
-        else { prep(k_render<true, false>, smem_bytes); k_render<true, false><<<grid, CTA_THREADS, smem_bytes, st>>>(a); }
+        if (count) { prep(k_render<true, true>, smem_bytes); k_render<true, true><<<grid, RENDER_THREADS, smem_bytes, st>>>(a); }
+        else { prep(k_render<true, false>, smem_bytes); k_render<true, false><<<grid, RENDER_THREADS, smem_bytes, st>>>(a); }
     } else {
-        if (count) k_render<false, true><<<grid, CTA_THREADS, 0, st>>>(a);
-        else k_render<false, false><<<grid, CTA_THREADS, 0, st>>>(a);
+        if (count) k_render<false, true><<<grid, RENDER_THREADS, 0, st>>>(a);
+        else k_render<false, false><<<grid, RENDER_THREADS, 0, st>>>(a);
     }
     return cudaGetLastError();
 }
