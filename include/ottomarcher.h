@@ -265,6 +265,13 @@ OM_API om_status om_render_elapsed_ms(om_render* r, float* ms, uint32_t* launche
 OM_API om_status om_render_read_pixels(om_render* r, om_pixel* host, size_t n);
 /* MODE_NORMAL view (main.rs:374-381): tightly packed RGB24, width*height*3 bytes.             */
 OM_API om_status om_render_read_rgb(om_render* r, uint8_t* host_rgb, size_t nbytes);
+/* One refresh of the viewer's pixel buffer (draw_to_sdl, main.rs:361-437) computed on the device: tightly
+ * packed RGB24.  mode 0 MODE_NORMAL, 1 MODE_SHOW_SAMPLES, 2 MODE_SAMPLE_WEIGHTED_BLUR, 3 MODE_SHOW_DEPTH,
+ * 4 MODE_DEPTH_WEIGHTED_BLUR, 5 MODE_SHOW_IDS, 6 MODE_ID_WEIGHTED_BLUR (the 3x3 cross-weighted filters of
+ * main.rs:219-343; they need width, height >= 3).  The SDL window itself is not part of this library. */
+OM_API om_status om_render_read_view(om_render* r, uint32_t mode, uint8_t* host_rgb, size_t nbytes);
+/* F12 of the viewer (surface.save_bmp, main.rs:473-476): 24-bit BMP of an RGB24 buffer.             */
+OM_API om_status om_write_bmp(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height);
 /* reset every pixel to Pixel::new() (render_thread.rs:47-50) and the counters to 0.           */
 OM_API om_status om_render_reset(om_render* r);
 

@@ -50,6 +50,7 @@ def lib():
     L.omo_scene_get_marched_tori.argtypes = [vp, P(A.MarchedTorus)]
     L.omo_render.argtypes = [vp, P(A.Camera), P(A.RenderParams), vp, vp, u32, u32, P(u64), P(u64), P(u64)]
     L.omo_render.restype = C.c_int
+    L.omo_view.argtypes = [C.c_int, vp, C.c_int, C.c_int, vp]
     L.omo_primary_rays.argtypes = [P(A.Camera), P(A.RenderParams), u32, u32, vp, vp]
     L.omo_primary.argtypes = [vp, P(A.Camera), P(A.RenderParams), u32, u32, vp, vp]
     L.omo_trace_rays.argtypes = [vp, vp, vp, sz, f32, f32, vp, vp, vp, vp]
@@ -194,6 +195,14 @@ class OracleScene:
         if want_counters:
             out["counters"] = dict(zip(["segments", "traced_tests", "sdf_evals", "normal_evals", "march_steps"], counters))
         return out
+
+
+def view(pixels, width, height, mode):
+    """draw_to_sdl's pixel buffer for one display mode (main.rs:361-437) from a Vec<Pixel>."""
+    px = np.ascontiguousarray(pixels)
+    rgb = np.zeros((height, width, 3), np.uint8)
+    lib().omo_view(mode, px.ctypes.data, width, height, rgb.ctypes.data)
+    return rgb
 
 
 def primary_rays(cam, params, mode=0, sample_index=0):

@@ -9,6 +9,7 @@
 
 #include "../include/ottomarcher.h"
 #include "ref_render.hpp"
+#include "ref_view.hpp"
 
 using namespace ref;
 
@@ -253,6 +254,7 @@ OMO_API void omo_scatter(const om_material* m, const float* in_orig, const float
     ScatterResult s = scatter(hr.material, r, hr, g);
     put3(att, s.attenuation); put3(out_orig, s.ray.orig); put3(out_dir, s.ray.dir);
 }
+OMO_API void omo_view(int mode, const om_pixel* px, int W, int H, uint8_t* rgb) { view(mode, px, W, H, rgb); }
 OMO_API uint32_t omo_hardware_threads() { unsigned n = std::thread::hardware_concurrency(); return n ? n : 1; }
 OMO_API const char* omo_version() { return "om_oracle 0.1 (C++ restatement of octaviogarcia/RaytracingOneWeekend; parity unpinned)"; }
 

@@ -48,6 +48,8 @@ PROTOTYPES = {
     "om_render_elapsed_ms": ("st", [vp, P(f32), P(u32)]),
     "om_render_read_pixels": ("st", [vp, vp, sz]),
     "om_render_read_rgb": ("st", [vp, vp, sz]),
+    "om_render_read_view": ("st", [vp, u32, vp, sz]),
+    "om_write_bmp": ("st", [C.c_char_p, vp, u32, u32]),
     "om_render_reset": ("st", [vp]),
     "om_render_primary": ("st", [vp, u32, u32, vp, vp, sz]),
     "om_render_export_accum": ("st", [vp, vp, vp]),

@@ -324,6 +324,13 @@ class Renderer:
         _lib.call("om_render_read_rgb", self.h, rgb.ctypes.data, rgb.nbytes)
         return rgb
 
+    def read_view(self, mode):
+        """One refresh of draw_to_sdl's buffer (main.rs:361-437): mode 0 normal, 1 samples, 2 sample-weighted
+        blur, 3 depth, 4 depth-weighted blur, 5 ids, 6 id-weighted blur."""
+        rgb = np.zeros((self.params.height, self.params.width, 3), np.uint8)
+        _lib.call("om_render_read_view", self.h, mode, rgb.ctypes.data, rgb.nbytes)
+        return rgb
+
     def primary(self, mode=0, sample_index=0):
         ids = np.zeros(self.npx, np.uint64); t = np.zeros(self.npx, np.float32)
         _lib.call("om_render_primary", self.h, mode, sample_index, ids.ctypes.data, t.ctypes.data, self.npx)
@@ -348,6 +355,12 @@ def render(camera, world, max_depth, tmin, tmax, samples_per_pixel, image_width,
         return r.read_pixels(), r.samples_done()
     finally:
         r.close()
+
+
+def write_bmp(path, rgb):
+    """F12 of the viewer (main.rs:473-476): save an RGB24 image as .bmp."""
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    _lib.call("om_write_bmp", str(path).encode(), rgb.ctypes.data, rgb.shape[1], rgb.shape[0])
 
 
 def bloom_get_hash(obj_id):

@@ -89,6 +89,104 @@ __global__ void k_compact_live(const float4* __restrict__ acc, const uint4* __re
     base = __shfl_sync(0xffffffffu, base, 0);
     if (live) list[base + __popc(m & ((1u << lane) - 1u))] = i;
 }
+// ---- draw_to_sdl's display modes (main.rs:361-437) and its three weighted 3x3 filters (main.rs:219-343) ----
+// reductions of MODE_SHOW_SAMPLES / MODE_SHOW_DEPTH: red[0] = max n (starts at 1), red[1] = bits of the largest finite
+// avg_depth >= 0 (bits order like values there), red[2] = 1 if one was seen (else the reference keeps -1)
+__global__ void k_view_reduce(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t npx, uint32_t* __restrict__ red) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    uint32_t n = 1u, dbits = 0u, seen = 0u;
+    if (i < npx) {
+        n = max(1u, __float_as_uint(acc[i].w));
+        const float d = __uint_as_float(aux[i].x);
+        if (d > -1.f && !isinf(d)) { seen = 1u; dbits = d > 0.f ? __float_as_uint(d) : 0u; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n = max(n, __shfl_xor_sync(0xffffffffu, n, o));
+        dbits = max(dbits, __shfl_xor_sync(0xffffffffu, dbits, o));
+        seen |= __shfl_xor_sync(0xffffffffu, seen, o);
+    }
+    if ((threadIdx.x & 31u) == 0u) { atomicMax(&red[0], n); if (seen) { atomicMax(&red[1], dbits); atomicOr(&red[2], 1u); } }
+}
+struct ViewPx {
+    float sx, sy, sz, n, depth;
+    unsigned long long bloom;
+};
+__device__ __forceinline__ ViewPx view_px(const float4* acc, const uint4* aux, uint32_t i) {
+    const float4 a = acc[i];
+    const uint4 x = aux[i];
+    ViewPx p;
+    p.sx = a.x; p.sy = a.y; p.sz = a.z; p.n = (float)__float_as_uint(a.w); p.depth = __uint_as_float(x.x);
+    p.bloom = ((unsigned long long)x.w << 32) | x.z;
+    return p;
+}
+__device__ __forceinline__ uint32_t view_tone(float r, float g, float b) {  // normalize_color(..).to_u8x3()
+    return d_as_u8(fminf(fmaxf(sqrtf(r), 0.f), 0.999f) * 256.0f) | (d_as_u8(fminf(fmaxf(sqrtf(g), 0.f), 0.999f) * 256.0f) << 8) |
+           (d_as_u8(fminf(fmaxf(sqrtf(b), 0.f), 0.999f) * 256.0f) << 16);
+}
+__global__ void k_view(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint8_t* __restrict__ rgb, uint32_t W, uint32_t H, uint32_t mode,
+                       const uint32_t* __restrict__ red) {
+    const uint32_t idx = blockIdx.x * UT + threadIdx.x;
+    if (idx >= W * H) return;
+    const int i = (int)(idx % W), j = (int)(idx / W);
+    uint32_t c = 0;
+    if (mode == 0u) {  // MODE_NORMAL
+        uint32_t cc[3];
+        d_color(acc[idx], cc);
+        c = cc[0] | (cc[1] << 8) | (cc[2] << 16);
+    } else if (mode == 1u) {  // MODE_SHOW_SAMPLES main.rs:383-398
+        const float smpls = (float)__float_as_uint(acc[idx].w) / (float)red[0];
+        c = view_tone(smpls, smpls, smpls);
+    } else if (mode == 3u) {  // MODE_SHOW_DEPTH main.rs:399-418
+        const float max_depth = red[2] ? __uint_as_float(red[1]) : -1.f;
+        const float depth_0to1 = __uint_as_float(aux[idx].x) / max_depth;
+        const bool is_inf = isinf(depth_0to1);
+        c = view_tone(is_inf ? 0.f : depth_0to1, is_inf ? 1.f : depth_0to1, is_inf ? 0.f : depth_0to1);
+    } else if (mode == 5u) {  // MODE_SHOW_IDS main.rs:428-436, utils.rs:45-69
+        const uint4 x = aux[idx];
+        const unsigned long long st = ((unsigned long long)x.w << 32) | x.z;
+        unsigned long long id1 = st & 0xFFFFFFFFull;
+        id1 ^= id1 << 13; id1 ^= id1 >> 7; id1 ^= id1 << 17;
+        unsigned long long id2 = st >> 32;
+        id2 ^= id2 << 13; id2 ^= id2 >> 17; id2 ^= id2 << 5;
+        const unsigned long long id = (id2 << 32) ^ id1 ^ (id1 * id2);
+        uint32_t b[8];
+        for (int k = 0; k < 8; k++) b[k] = (uint32_t)((id >> (8 * k)) & 0xFFull);
+        c = (b[0] ^ b[7] ^ b[3]) | ((b[1] ^ b[4] ^ b[5]) << 8) | ((b[2] ^ b[6]) << 16);
+    } else {  // the weighted 3x3 filters: 2 samples, 4 depth, 6 ids (apply_box_filter_ij_*, main.rs:222-318)
+        const int min_x = i == 0 ? 0 : -1, max_x = i == (int)W - 1 ? 0 : 1, min_y = j == 0 ? 0 : -1, max_y = j == (int)H - 1 ? 0 : 1;  // main.rs:324-342
+        const ViewPx ctr = view_px(acc, aux, idx);
+        const float SQRT2_INV = 0.7071067811865475244f;
+        if (mode == 4u && isinf(ctr.depth)) {
+            uint32_t cc[3];
+            d_color(acc[idx], cc);
+            c = cc[0] | (cc[1] << 8) | (cc[2] << 16);
+        } else {
+            float total_weight = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+            for (int y = min_y; y <= max_y; y++) {
+                for (int x = min_x; x <= max_x; x++) {
+                    const ViewPx q = view_px(acc, aux, (uint32_t)((i + x) + (j + y) * (int)W));
+                    const float is_diagonal = (x != 0 && y != 0) ? 1.f : 0.f;
+                    if (mode == 2u) {
+                        const float diag_w = 1.f - (1.f - SQRT2_INV) * is_diagonal;
+                        total_weight += q.n * diag_w;
+                        cr = cr + q.sx * diag_w; cg = cg + q.sy * diag_w; cb = cb + q.sz * diag_w;
+                    } else {
+                        float w;
+                        if (mode == 4u) w = 1.f / (1.f + fabsf(q.depth - ctr.depth));
+                        else w = ((q.bloom == ctr.bloom) ? 1.f : 0.f) + (((q.bloom & ctr.bloom) == ctr.bloom) ? 1.f : 0.f);
+                        const float diag_w = w * (1.f - (1.f - SQRT2_INV) * is_diagonal);
+                        total_weight += diag_w;
+                        const float inv_n = 1.f / q.n;  // Div<f32> = multiply by the reciprocal
+                        cr = cr + diag_w * (q.sx * inv_n); cg = cg + diag_w * (q.sy * inv_n); cb = cb + diag_w * (q.sz * inv_n);
+                    }
+                }
+            }
+            const float inv_w = 1.f / total_weight;
+            c = view_tone(cr * inv_w, cg * inv_w, cb * inv_w);
+        }
+    }
+    rgb[3u * idx] = (uint8_t)(c & 0xFFu); rgb[3u * idx + 1] = (uint8_t)((c >> 8) & 0xFFu); rgb[3u * idx + 2] = (uint8_t)((c >> 16) & 0xFFu);
+}
 // dependent-free FMA chains: the FP32 roofline denominator
 __global__ void k_fma_peak(float* out, int iters) {
     float a[8];
@@ -520,6 +618,49 @@ om_status om_render_read_rgb(om_render* r, uint8_t* host_rgb, size_t nbytes) {
     CU(cudaMemcpyAsync(host_rgb, r->staging, nbytes, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaStreamSynchronize(r->stream));
     return OM_OK;
+}
+
+om_status om_render_read_view(om_render* r, uint32_t mode, uint8_t* host_rgb, size_t nbytes) {
+    if (!r || !host_rgb) return fail(OM_ERR_INVALID, "om_render_read_view: NULL argument");
+    if (mode > 6u) return fail(OM_ERR_INVALID, "om_render_read_view: mode must be 0..6 (main.rs:361-368)");
+    if (nbytes != size_t(r->npx) * 3u) return fail(OM_ERR_INVALID, "om_render_read_view: nbytes must be width*height*3");
+    if ((mode == 2u || mode == 4u || mode == 6u) && (r->p.width < 3u || r->p.height < 3u))
+        return fail(OM_ERR_INVALID, "om_render_read_view: the 3x3 filters need an image of at least 3x3 (the reference's border loops, main.rs:324-342)");
+    CU(cudaSetDevice(r->dev));
+    om_status s = ensure_staging(r, nbytes + 16u);
+    if (s != OM_OK) return s;
+    uint32_t* red = (uint32_t*)((uint8_t*)r->staging + ((nbytes + 3u) & ~size_t(3)));
+    const uint32_t init[3] = {1u, 0u, 0u};
+    CU(cudaMemcpyAsync(red, init, sizeof init, cudaMemcpyHostToDevice, r->stream));
+    if (mode == 1u || mode == 3u) {
+        k_view_reduce<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, red);
+        CU(cudaGetLastError());
+    }
+    k_view<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, (uint8_t*)r->staging, r->p.width, r->p.height, mode, red);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(host_rgb, r->staging, nbytes, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+
+om_status om_write_bmp(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height) {
+    if (!path || !rgb || !width || !height) return fail(OM_ERR_INVALID, "om_write_bmp: bad argument");
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(OM_ERR_INVALID, "om_write_bmp: cannot open %s", path);
+    const uint32_t row = (width * 3u + 3u) & ~3u, data = row * height, off = 54u, size = off + data;
+    uint8_t h[54] = {0};
+    auto put32 = [&](int o, uint32_t v) { h[o] = uint8_t(v); h[o + 1] = uint8_t(v >> 8); h[o + 2] = uint8_t(v >> 16); h[o + 3] = uint8_t(v >> 24); };
+    h[0] = 'B'; h[1] = 'M'; put32(2, size); put32(10, off); put32(14, 40u); put32(18, width); put32(22, height);
+    h[26] = 1; h[28] = 24; put32(34, data); put32(38, 2835u); put32(42, 2835u);
+    bool ok = fwrite(h, 1, 54, f) == 54;
+    std::vector<uint8_t> line(row, 0);
+    for (uint32_t y = 0; ok && y < height; y++) {  // BMP rows run bottom-up, pixels are BGR
+        const uint8_t* src = rgb + size_t(height - 1 - y) * width * 3u;
+        for (uint32_t x = 0; x < width; x++) { line[3 * x] = src[3 * x + 2]; line[3 * x + 1] = src[3 * x + 1]; line[3 * x + 2] = src[3 * x]; }
+        ok = fwrite(line.data(), 1, row, f) == row;
+    }
+    ok = (fclose(f) == 0) && ok;
+    return ok ? OM_OK : fail(OM_ERR_INVALID, "om_write_bmp: write to %s failed", path);
 }
 
 om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_index, uint64_t* ids, float* t, size_t n) {

@@ -322,3 +322,35 @@ def test_pipeline_flags_exclusive(api, A, rtiow):
     fz, _ = rtiow
     with pytest.raises(Exception):
         api.Renderer(fz, cam_rtiow(api), api.render_params(16, 16, 1, flags=A.RENDER_PERSISTENT | A.RENDER_WAVEFRONT))
+
+
+# ---- the viewer's display modes and 3x3 weighted filters (main.rs:219-343, 361-437) on the device ----
+@pytest.mark.parametrize("W,H,adaptive", [(64, 48, False), (37, 23, True), (3, 3, False)])
+def test_view_modes_bit_exact(api, A, O, rtiow, W, H, adaptive, tmp_path):
+    fz, _ = rtiow
+    cam = cam_rtiow(api, W / H)
+    r = api.Renderer(fz, cam, api.render_params(W, H, 24, seed=3, flags=A.RENDER_ADAPTIVE if adaptive else 0))
+    r.launch(0); r.sync()
+    px = r.read_pixels()
+    for mode in range(7):
+        g = r.read_view(mode)
+        assert (g == O.view(px, W, H, mode)).all(), "display mode %d" % mode
+    assert (r.read_view(0) == r.read_rgb()).all()
+    api.write_bmp(tmp_path / "f12.bmp", r.read_view(0))
+    raw = (tmp_path / "f12.bmp").read_bytes()
+    assert raw[:2] == b"BM" and len(raw) == 54 + ((3 * W + 3) // 4 * 4) * H
+    # bottom-up BGR rows: the first stored row is the last image row
+    assert raw[54:57] == bytes(r.read_view(0)[H - 1, 0, ::-1])
+    r.close()
+
+
+def test_view_rejects_bad_arguments(api, A, rtiow):
+    fz, _ = rtiow
+    r = api.Renderer(fz, cam_rtiow(api, 1.0), api.render_params(2, 2, 1))
+    r.launch(0); r.sync()
+    with pytest.raises(Exception):
+        r.read_view(7)
+    with pytest.raises(Exception):
+        r.read_view(2)  # 3x3 filter on a 2x2 image
+    assert r.read_view(0).shape == (2, 2, 3)
+    r.close()

@@ -213,3 +213,27 @@ def test_render_counters_and_determinism(api, O, A):
     d = s.render(cam, pa, nthreads=2)
     assert d["credited"] == 24 * 16 * 64 and d["traced"] < d["credited"]
     assert ((d["pixels"]["bad_avgs"] >= 5) | (d["pixels"]["n"] == 64)).all()
+
+
+def test_view_modes_known_answers(O, A):
+    """Display modes of main.rs:361-437 on hand-made pixel buffers."""
+    import numpy as np
+    W, H = 4, 3
+    px = np.zeros(W * H, dtype=A.PIXEL_DTYPE)
+    px["n"] = 4
+    px["sum"] = np.array([1.0, 0.3, 0.0], np.float32) * 4   # average colour (1, 0.3, 0): sqrt(.3) * 256 = 140.2, far from a rounding edge
+    px["color"] = np.array([255, 140, 0], np.uint8)         # sqrt, clamp .999, *256
+    px["avg_depth"] = 2.0
+    px["bloom"] = 0
+    assert (O.view(px, W, H, 0) == px["color"].reshape(H, W, 3)).all()
+    assert (O.view(px, W, H, 1) == 255).all()                      # n / max n = 1 -> .999 * 256
+    assert (O.view(px, W, H, 3) == 255).all()                      # depth / max depth = 1
+    assert (O.view(px, W, H, 5) == 0).all()                        # scramble(0) = 0 -> black
+    for mode in (2, 4, 6):                                         # any weighted mean of a constant image is that image
+        assert (O.view(px, W, H, mode) == px["color"].reshape(H, W, 3)).all(), mode
+    px["avg_depth"][5] = np.inf                                    # sky pixel: depth view paints it green, depth blur copies its colour
+    v3 = O.view(px, W, H, 3)
+    assert tuple(v3[1, 1]) == (0, 255, 0)
+    assert tuple(O.view(px, W, H, 4)[1, 1]) == (255, 140, 0)
+    px["n"][0] = 1                                                 # quarter of the samples -> sqrt(.25) * 256 = 128
+    assert tuple(O.view(px, W, H, 1)[0, 0]) == (128, 128, 128)
