@@ -234,8 +234,9 @@ OM_API om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out,
 OM_API om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags);
 /* statistics of the frozen scene: [0] bvh nodes, [1] bvh depth, [2] primitives in the BVH,
  * [3] primitives kept in the always-test list, [4] bytes of the device scene image,
- * [5] 1 if that image fits in shared memory */
-OM_API om_status om_scene_stats(const om_scene* s, uint64_t stats[6]);
+ * [5] 1 if the hot part of that image fits in shared memory, [6] cells of the marched-object candidate grid
+ * (0 = no grid), [7] entries in its lists (rounded up to 4) */
+OM_API om_status om_scene_stats(const om_scene* s, uint64_t stats[8]);
 
 /* ------------------------------------------------------------------------------------------ */
 /* render: render_thread::render (render_thread.rs:145-202)                                    */

@@ -250,9 +250,9 @@ class FrozenHittableList:
         return out
 
     def stats(self):
-        s = (C.c_uint64 * 6)()
+        s = (C.c_uint64 * 8)()
         _lib.call("om_scene_stats", self.h, s)
-        return dict(zip(["bvh_nodes", "bvh_depth", "bvh_prims", "always_test", "device_bytes", "fits_smem"], s))
+        return dict(zip(["bvh_nodes", "bvh_depth", "bvh_prims", "always_test", "device_bytes", "fits_smem", "mgrid_cells", "mgrid_entries"], s))
 
     def hit(self, origins, dirs, t_min=0.001, t_max=100.0, flags=0, device=-1):
         """FrozenHittableList::hit (hits.rs:270-334) for a batch of rays -> (obj_id, t, point, normal)."""

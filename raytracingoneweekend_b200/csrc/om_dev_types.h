@@ -47,6 +47,13 @@ struct SceneHeader {
     // object and cannot start inside one.  lo > hi when the scene has no marched object.
     float march_lo[3], march_hi[3];
     uint32_t n_marched;
+    // Candidate grid over the marched objects (0 cells = none): cell (ix,iy,iz) of the box starting at mgrid_lo with
+    // edge 1/mgrid_inv_h lists, in the reference's order, every marched object that can attain min_j |sdf_j(p)| at some
+    // point p of the cell; all others are provably farther than some listed one everywhere in the cell, so skipping
+    // them leaves both the minimum and the first object attaining it (hits.rs:301-311) unchanged.
+    // cold image: cells = uint2 {first, count} (2 per unit) at off_mgrid_cells, lists = j (4 per unit) at off_mgrid_lists
+    float mgrid_lo[3], mgrid_inv_h;
+    uint32_t mgrid_dim[3], off_mgrid_cells, off_mgrid_lists;
     uint32_t off_sph_mat;  // hot image: one byte per sphere = its material type (shade class of a hit, om_wavefront.cuh)
 };
 

@@ -448,6 +448,7 @@ __device__ __forceinline__ uint32_t marched_ref(const SceneHeader& S, uint32_t j
     return omd::make_ref(omd::PT_MTORUS, j - n_ms - n_mb);
 }
 struct Near {
+    uint32_t evals;  // SDFs evaluated (executed-work accounting)
     float d;       // min over the marched objects of |sdf(p)|
     uint32_t ref;  // the first object that attains it (strict `<`, hits.rs:304,345); REF_NONE if none
 };
@@ -456,6 +457,27 @@ __device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHead
     Near n;
     n.d = kInf;
     n.ref = omd::REF_NONE;
+    n.evals = S.n_marched;
+    if (S.mgrid_dim[0] != 0u) {
+        // inside the candidate grid only the cell's list is evaluated, in the same order: the objects left out are
+        // provably farther than a listed one everywhere in the cell (om_scene.cpp, build_marched_grid)
+        const float fx = (p.x - S.mgrid_lo[0]) * S.mgrid_inv_h, fy = (p.y - S.mgrid_lo[1]) * S.mgrid_inv_h, fz = (p.z - S.mgrid_lo[2]) * S.mgrid_inv_h;
+        if (fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < (float)S.mgrid_dim[0] && fy < (float)S.mgrid_dim[1] && fz < (float)S.mgrid_dim[2]) {
+            const uint32_t cell = ((uint32_t)fz * S.mgrid_dim[1] + (uint32_t)fy) * S.mgrid_dim[0] + (uint32_t)fx;
+            const float4 cc = sv.cold(S.off_mgrid_cells + (cell >> 1));
+            const uint32_t first = __float_as_uint((cell & 1u) ? cc.z : cc.x), count = __float_as_uint((cell & 1u) ? cc.w : cc.y);
+            n.evals = count;
+            for (uint32_t k = first; k < first + count; k++) {
+                const float4 l4 = sv.cold(S.off_mgrid_lists + (k >> 2));
+                const uint32_t sel = k & 3u;
+                const uint32_t j = __float_as_uint(sel == 0u ? l4.x : (sel == 1u ? l4.y : (sel == 2u ? l4.z : l4.w)));
+                const uint32_t ref = marched_ref(S, j);
+                const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+                if (d < n.d) { n.d = d; n.ref = ref; }
+            }
+            return n;
+        }
+    }
     for (uint32_t j = 0; j < S.n_marched; j++) {
         const uint32_t ref = marched_ref(S, j);
         const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
@@ -491,7 +513,7 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
         const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
         float new_t = t_min;
         const Near n0 = nearest_marched(sv, S, ray_at(r, t_min));
-        if (COUNT) cn->sdf_evals += S.n_marched;
+        if (COUNT) cn->sdf_evals += n0.evals;
         if (n0.ref == omd::REF_NONE) return out;  // `marched.is_none()` -> INF -> return rec (also every NaN ray)
         float aux = n0.d;
         int steps = 0;
@@ -509,7 +531,7 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
         max_march_iter--;
         const V3 point = ray_at(r, t);
         const Near n = nearest_marched(sv, S, point);
-        if (COUNT) { cn->march_steps++; cn->sdf_evals += S.n_marched; }
+        if (COUNT) { cn->march_steps++; cn->sdf_evals += n.evals; }
         if (n.ref == omd::REF_NONE) return out;  // `material.is_none()`
         if (n.d < HIT_SIZE) {
             // The reference evaluates the normal of the nearest object at every step

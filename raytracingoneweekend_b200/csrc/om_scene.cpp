@@ -102,6 +102,137 @@ void pack_material(Packer& p, const om_material& m, uint32_t pt, size_t index) {
     p.f4(m.albedo[0], m.albedo[1], m.albedo[2], m.fuzz);
     p.f4(m.ior, u2f(m.mat_type), u2f(uint32_t(bloom)), u2f(uint32_t(bloom >> 32)));
 }
+
+// ---- candidate grid over the marched objects (see SceneHeader::mgrid_*) -------------------------------------
+// Bounds, over an axis-aligned cell, of the value the reference computes for |Marched::sdf| (marched.rs:14-18),
+// in double with margins far above f32 rounding.
+struct MBound { double lb, ub; };
+double box_point_dist(const double lo[3], const double hi[3], const double c[3], bool farthest) {
+    double s = 0;
+    for (int a = 0; a < 3; a++) {
+        double d;
+        if (farthest) d = std::max(std::fabs(c[a] - lo[a]), std::fabs(c[a] - hi[a]));
+        else d = c[a] < lo[a] ? lo[a] - c[a] : (c[a] > hi[a] ? c[a] - hi[a] : 0.0);
+        s += d * d;
+    }
+    return std::sqrt(s);
+}
+MBound loosen(double lb, double ub, double scale) {
+    MBound b;
+    b.lb = std::max(0.0, lb * (1 - 1e-4) - 1e-5 * (1 + scale));
+    b.ub = ub * (1 + 1e-4) + 1e-5 * (1 + scale);
+    return b;
+}
+MBound msphere_bound(const om_marched_sphere& s, const double lo[3], const double hi[3]) {  // | |p - c| - r |
+    const double c[3] = {s.center[0], s.center[1], s.center[2]}, r = s.radius;
+    const double dmin = box_point_dist(lo, hi, c, false), dmax = box_point_dist(lo, hi, c, true);
+    const double lb = (r >= dmin && r <= dmax) ? 0.0 : std::min(std::fabs(dmin - r), std::fabs(dmax - r));
+    return loosen(lb, std::max(std::fabs(dmin - r), std::fabs(dmax - r)), std::fabs(r) + dmax);
+}
+MBound mbox_bound(const om_marched_box& s, const double lo[3], const double hi[3]) {  // marched.rs:86-89, convex in p
+    auto sdf = [&](const double p[3]) {
+        double q[3], o = 0, in = -1e300;
+        for (int a = 0; a < 3; a++) { q[a] = std::fabs(p[a] - s.center[a]) - s.sizes[a]; o += std::max(q[a], 0.0) * std::max(q[a], 0.0); in = std::max(in, q[a]); }
+        return std::sqrt(o) + std::min(in, 0.0);
+    };
+    double blo[3], bhi[3], gap = 0, mx = -1e300, deepest = 1e300, ext = 0;
+    for (int a = 0; a < 3; a++) {
+        blo[a] = s.center[a] - std::fabs(s.sizes[a]); bhi[a] = s.center[a] + std::fabs(s.sizes[a]);
+        const double d = lo[a] > bhi[a] ? lo[a] - bhi[a] : (hi[a] < blo[a] ? blo[a] - hi[a] : 0.0);
+        gap += d * d;
+        deepest = std::min(deepest, std::fabs(double(s.sizes[a])));
+        ext = std::max(ext, std::max(std::fabs(lo[a]), std::fabs(hi[a])));
+    }
+    for (int k = 0; k < 8; k++) { const double p[3] = {k & 1 ? hi[0] : lo[0], k & 2 ? hi[1] : lo[1], k & 4 ? hi[2] : lo[2]}; mx = std::max(mx, sdf(p)); }
+    return loosen(std::sqrt(gap), std::max(mx, deepest), ext);  // cell touching the box: lb = 0; inside, |sdf| <= smallest half size
+}
+MBound mtorus_bound(const om_marched_torus& s, const double lo[3], const double hi[3]) {
+    // q = W2L_TR * (p * w2l_scale) (marched.rs:142-144): affine; value = local_sdf(q) * min l2w scale (marched.rs:148-150)
+    const float* m = s.m_world_to_local_translate_rotate;
+    const float* si = s.m_world_to_local_scale;
+    double pc[3], half = 0, smax = 0;
+    for (int a = 0; a < 3; a++) { pc[a] = 0.5 * (lo[a] + hi[a]); half += 0.25 * (hi[a] - lo[a]) * (hi[a] - lo[a]); smax = std::max(smax, std::fabs(double(si[a]))); }
+    // operator norm of the linear part <= |rotation rows| * max scale (rows of a TR matrix are unit, but be safe)
+    double rown = 0;
+    for (int r = 0; r < 3; r++) rown = std::max(rown, std::sqrt(double(m[4 * r]) * m[4 * r] + double(m[4 * r + 1]) * m[4 * r + 1] + double(m[4 * r + 2]) * m[4 * r + 2]));
+    const double rho = std::sqrt(half) * smax * rown * 1.7320508;
+    double q0[3], n0 = 0;
+    for (int r = 0; r < 3; r++) {
+        q0[r] = m[4 * r] * (pc[0] * si[0]) + m[4 * r + 1] * (pc[1] * si[1]) + m[4 * r + 2] * (pc[2] * si[2]) + m[4 * r + 3] * double(si[3]);
+        n0 += q0[r] * q0[r];
+    }
+    n0 = std::sqrt(n0);
+    const double ball = std::fabs(double(s.sizes[0])) + std::fabs(double(s.sizes[1]));
+    const double mins = std::fabs(double(fminf(s.m_local_to_world_scale[0], fminf(s.m_local_to_world_scale[1], s.m_local_to_world_scale[2]))));
+    return loosen(mins * std::max(0.0, n0 - rho - ball), mins * (n0 + rho + ball), mins * (n0 + rho + ball));
+}
+
+void build_marched_grid(const omh::SceneLists& L, omd::SceneHeader& h, Packer& cold) {
+    const size_t ns = L.marched_spheres.size(), nb = L.marched_boxes.size(), nt = L.marched_tori.size(), n = ns + nb + nt;
+    for (int a = 0; a < 3; a++) { h.mgrid_lo[a] = 0.f; h.mgrid_dim[a] = 0u; }
+    h.mgrid_inv_h = 0.f; h.off_mgrid_cells = 0u; h.off_mgrid_lists = 0u;
+    if (n < 6) return;  // a handful of objects: the plain loop is as fast
+    // world extent (centre, radius) of each object; the grid covers the typical ones, not a scene-sized ground
+    std::vector<double> cx(n), cy(n), cz(n), rad(n);
+    for (size_t i = 0; i < ns; i++) { const auto& s = L.marched_spheres[i]; cx[i] = s.center[0]; cy[i] = s.center[1]; cz[i] = s.center[2]; rad[i] = std::fabs(double(s.radius)); }
+    for (size_t i = 0; i < nb; i++) { const auto& s = L.marched_boxes[i]; const size_t j = ns + i; cx[j] = s.center[0]; cy[j] = s.center[1]; cz[j] = s.center[2]; rad[j] = std::sqrt(double(s.sizes[0]) * s.sizes[0] + double(s.sizes[1]) * s.sizes[1] + double(s.sizes[2]) * s.sizes[2]); }
+    for (size_t i = 0; i < nt; i++) {
+        const auto& s = L.marched_tori[i]; const size_t j = ns + nb + i;
+        const float* m = s.m_local_to_world_translate_rotate; const float* sc = s.m_local_to_world_scale;
+        cx[j] = double(m[3]) * sc[0]; cy[j] = double(m[7]) * sc[1]; cz[j] = double(m[11]) * sc[2];
+        rad[j] = (std::fabs(double(s.sizes[0])) + std::fabs(double(s.sizes[1]))) * std::max(std::fabs(double(sc[0])), std::max(std::fabs(double(sc[1])), std::fabs(double(sc[2]))));
+    }
+    std::vector<double> sorted(rad);
+    std::sort(sorted.begin(), sorted.end());
+    const double med = std::max(sorted[n / 2], 1e-6);
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    size_t typical = 0;
+    for (size_t j = 0; j < n; j++) {
+        if (!(rad[j] <= 20 * med) || !std::isfinite(cx[j] + cy[j] + cz[j])) continue;
+        typical++;
+        const double c[3] = {cx[j], cy[j], cz[j]};
+        for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], c[a] - rad[j]); hi[a] = std::max(hi[a], c[a] + rad[j]); }
+    }
+    if (typical < 4) return;
+    // rays spend many march steps around the objects too (arriving from the camera, leaving towards the sky): the grid
+    // covers the objects' box plus half its largest extent on every side
+    double vol = 1, ext = 0;
+    for (int a = 0; a < 3; a++) ext = std::max(ext, hi[a] - lo[a]);
+    for (int a = 0; a < 3; a++) { lo[a] -= std::max(2 * med, 0.5 * ext); hi[a] += std::max(2 * med, 0.5 * ext); vol *= (hi[a] - lo[a]); }
+    double edge = std::max(1.5 * med, std::cbrt(vol / 100000.0));
+    uint32_t dim[3];
+    for (int a = 0; a < 3; a++) dim[a] = uint32_t(std::min(1024.0, std::max(1.0, std::ceil((hi[a] - lo[a]) / edge))));
+    const float flo[3] = {float(lo[0]), float(lo[1]), float(lo[2])};
+    const float inv_h = float(1.0 / edge);
+    const size_t ncell = size_t(dim[0]) * dim[1] * dim[2];
+    std::vector<uint32_t> first(ncell), count(ncell), lists;
+    std::vector<MBound> bnd(n);
+    for (uint32_t iz = 0; iz < dim[2]; iz++) for (uint32_t iy = 0; iy < dim[1]; iy++) for (uint32_t ix = 0; ix < dim[0]; ix++) {
+        // the device maps p to a cell with f32 arithmetic: (p - lo) * inv_h, truncated; make the cell's box a bit larger
+        const uint32_t id[3] = {ix, iy, iz};
+        double clo[3], chi[3];
+        for (int a = 0; a < 3; a++) {
+            const double e = 1.0 / double(inv_h), slack = 1e-4 * e + 1e-5 * (1 + std::fabs(double(flo[a])) + e * dim[a]);
+            clo[a] = double(flo[a]) + id[a] * e - slack; chi[a] = double(flo[a]) + (id[a] + 1) * e + slack;
+        }
+        double u = 1e300;
+        for (size_t j = 0; j < n; j++) {
+            bnd[j] = j < ns ? msphere_bound(L.marched_spheres[j], clo, chi) : (j < ns + nb ? mbox_bound(L.marched_boxes[j - ns], clo, chi) : mtorus_bound(L.marched_tori[j - ns - nb], clo, chi));
+            if (bnd[j].ub == bnd[j].ub) u = std::min(u, bnd[j].ub);
+        }
+        const size_t cell = (size_t(iz) * dim[1] + iy) * dim[0] + ix;
+        first[cell] = uint32_t(lists.size());
+        for (size_t j = 0; j < n; j++)
+            if (!(bnd[j].lb > u)) lists.push_back(uint32_t(j));  // (a NaN bound keeps the object)
+        count[cell] = uint32_t(lists.size()) - first[cell];
+    }
+    for (int a = 0; a < 3; a++) { h.mgrid_lo[a] = flo[a]; h.mgrid_dim[a] = dim[a]; }
+    h.mgrid_inv_h = inv_h;
+    h.off_mgrid_cells = cold.units();
+    for (size_t c = 0; c < ncell; c += 2) cold.u4(first[c], count[c], c + 1 < ncell ? first[c + 1] : 0u, c + 1 < ncell ? count[c + 1] : 0u);
+    h.off_mgrid_lists = cold.units();
+    for (size_t k = 0; k < lists.size(); k += 4) cold.u4(lists[k], k + 1 < lists.size() ? lists[k + 1] : 0u, k + 2 < lists.size() ? lists[k + 2] : 0u, k + 3 < lists.size() ? lists[k + 3] : 0u);
+}
 }  // namespace
 
 void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, FrozenScene& out) {
@@ -276,6 +407,7 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
     };
     mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
     mats(PT_PARA, L.parallelograms); mats(PT_MSPHERE, L.marched_spheres); mats(PT_MBOX, L.marched_boxes); mats(PT_MTORUS, L.marched_tori);
+    build_marched_grid(L, h, cold);
     if (cold.units() == 0) cold.f4(0, 0, 0, 0);
     if (hot.units() == 0) hot.f4(0, 0, 0, 0);
     h.hot_units = hot.units();

@@ -263,8 +263,8 @@ __device__ __noinline__ void wf_march_warp(const RenderArgs& A, const omk::WfArg
         int budget = steps;
         uint32_t code = __float_as_uint(hm.w);
         if (code == WF_NONE) {
-            if (COUNT) { cn.march_entered++; cn.sdf_evals += S.n_marched; }
             const Near n0 = nearest_marched(sv, S, ray_at(ray, A.tmin));
+            if (COUNT) { cn.march_entered++; cn.sdf_evals += n0.evals; }
             if (n0.ref == omd::REF_NONE) finished = true;  // `marched.is_none()` -> INF -> return rec (also every NaN ray)
             else if (n0.d < HIT_SIZE) { code = 0x80000000u | n0.ref; t_m = A.tmin; }
             else { code = 1024u; t_m = A.tmin; }
@@ -292,7 +292,7 @@ __device__ __noinline__ void wf_march_warp(const RenderArgs& A, const omk::WfArg
                 if (!(t_m < A.tmax && t_m < closest && iter > 0)) { finished = true; break; }
                 iter--;
                 const Near nn = nearest_marched(sv, S, ray_at(ray, t_m));
-                if (COUNT) { cn.march_steps++; cn.sdf_evals += S.n_marched; }
+                if (COUNT) { cn.march_steps++; cn.sdf_evals += nn.evals; }
                 if (nn.ref == omd::REF_NONE) { finished = true; break; }  // `material.is_none()`
                 if (nn.d < HIT_SIZE) {
                     // the reference evaluates the nearest object's normal at every step (hits.rs:306); only the

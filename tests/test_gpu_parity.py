@@ -354,3 +354,17 @@ def test_view_rejects_bad_arguments(api, A, rtiow):
         r.read_view(2)  # 3x3 filter on a 2x2 image
     assert r.read_view(0).shape == (2, 2, 3)
     r.close()
+
+
+def test_marched_candidate_grid_hit_bit_exact(api, A, O):
+    """65 marched objects: min_j |sdf_j| is taken over the candidate list of the point's grid cell
+    (om_scene.cpp build_marched_grid); ids, t, points and normals must stay those of the full loop."""
+    fz = api.FrozenHittableList.generate("marched", 3)
+    osc = oracle_scene_from(O, fz)
+    o, d = rays_at_scene(6000, 5, spread=9.0)
+    assert_hits_equal(fz.hit(o, d), osc.trace_rays(o, d))
+    rng = np.random.default_rng(6)   # rays born between the objects, every direction (also leaving the grid)
+    o2 = rng.uniform(-9, 9, (6000, 3)).astype(np.float32); o2[:, 1] = rng.uniform(0.0, 1.6, 6000)
+    d2 = rng.normal(0, 1, (6000, 3)).astype(np.float32)
+    assert_hits_equal(fz.hit(o2, d2), osc.trace_rays(o2, d2))
+    assert_hits_equal(fz.hit(o2, d2, flags=A.RENDER_NO_SMEM_SCENE), osc.trace_rays(o2, d2))
