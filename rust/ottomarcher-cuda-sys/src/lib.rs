@@ -17,6 +17,8 @@ pub const OM_RENDER_FAST_MATH: u32 = 1 << 1;
 pub const OM_RENDER_BRUTE_FORCE: u32 = 1 << 2;
 pub const OM_RENDER_NO_SMEM_SCENE: u32 = 1 << 4;
 pub const OM_RENDER_COUNTERS: u32 = 1 << 5;
+pub const OM_RENDER_WAVEFRONT: u32 = 1 << 3;
+pub const OM_RENDER_PERSISTENT: u32 = 1 << 6;
 
 /// materials.rs:11-23
 #[repr(C)] #[derive(Clone, Copy, Default)]
@@ -85,6 +87,8 @@ extern "C" {
     pub fn om_render_samples_traced(r: *mut om_render, traced: *mut u64) -> om_status;
     pub fn om_render_read_pixels(r: *mut om_render, host: *mut om_pixel, n: usize) -> om_status;
     pub fn om_render_read_rgb(r: *mut om_render, host_rgb: *mut u8, nbytes: usize) -> om_status;
+    pub fn om_render_read_view(r: *mut om_render, mode: u32, host_rgb: *mut u8, nbytes: usize) -> om_status;
+    pub fn om_write_bmp(path: *const c_char, rgb: *const u8, width: u32, height: u32) -> om_status;
     pub fn om_render_reset(r: *mut om_render) -> om_status;
     pub fn om_render_primary(r: *mut om_render, mode: u32, sample_index: u32, ids: *mut u64, t: *mut f32, n: usize) -> om_status;
     pub fn om_last_error() -> *const c_char;
