@@ -199,6 +199,7 @@ def run_ours(args):
         step()
     barrier()
     dr.r.elapsed_ms()  # drop warm-up launch timings
+    kernels0 = dr.r.perf_counters()["kernels"]
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -216,6 +217,9 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     kern_ms, kern_launches = dr.r.elapsed_ms()
+    pcs = dr.r.perf_counters()
+    kernels_timed = pcs["kernels"] - kernels0
+    wavefront = bool(pcs["flags"] & A.RENDER_WAVEFRONT)
     samples_step = W * H * spp
     value = samples_step * args.steps / (ms_total * 1e-3) / 1e6
     traced = dr.r.samples_traced()
@@ -274,7 +278,7 @@ def run_ours(args):
         achieved_tf = fps * samples_launch / (launch_ms * 1e-3) / 1e12
         roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf, "traffic": None,
                     "peak_source": "FMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
-                    "flops_per_sample": fps, "kernel": "k_wf_extend + k_wf_shade + k_wf_compact (+ k_render tail)" if args.wavefront else "k_render", "launch_ms": launch_ms,
+                    "flops_per_sample": fps, "kernel": "k_wf_extend + k_wf_shade + k_wf_compact (+ k_render tail)" if wavefront else "k_render", "launch_ms": launch_ms,
                     "per_sample": {k: c[k] / c["traced"] for k in ("segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals")},
                     "accumulate_hbm": {"bytes_per_launch": 64 * W * H, "note": "32 B read + 32 B write per pixel per launch"}}
         cpu = None
@@ -286,10 +290,11 @@ def run_ours(args):
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "%s: %s %dx%d, %d spp, depth %d, fixed spp" % (args.workload, kind, W, H, spp, MAX_DEPTH),
-                       "partition": "spp slices + 1 NCCL reduce" if world > 1 else "single GPU", "pipeline": "wavefront" if args.wavefront else "persistent kernel",
-                       "l2": "scene is 93 KB in shared memory; per-step traffic is the 66 MB framebuffer, rewritten by reset() every step"},
+                       "partition": "spp slices + 1 NCCL reduce" if world > 1 else "single GPU", "pipeline": ("wavefront" if wavefront else "persistent kernel") + ("" if args.wavefront else " (library's choice)"),
+                       "l2": "scene image %.1f MB %s; per-step traffic beyond it is the %d MB framebuffer, rewritten by reset() every step"
+                             % (fz.stats()["device_bytes"] / 1e6, "with its hot part in shared memory" if pcs["scene_in_smem"] else "read through L1/L2 (larger than shared memory)", W * H * 32 // 1000000)},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 40},
-            "gpu_launches": args.steps * (1 + (3 if world > 1 else 0)),
+            "gpu_launches": int(kernels_timed) + args.steps * (3 if world > 1 else 0),
             "clocks": clocks, "roofline": roofline, "samples_traced_rank0": traced,
         }
         if cpu:

@@ -230,11 +230,22 @@ OM_API om_status om_scene_counts(const om_scene* s, uint64_t counts[8]);
 OM_API om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out, size_t nbytes);
 /* HittableList::freeze (hits.rs:87-89).  Builds the BVH that subsumes CameraHash
  * (camera_hash.rs, hits.rs:116-185) from the objects' world bounding boxes
- * (bounding_box.rs:69-73).  `cam` may be NULL (the BVH does not depend on the camera).         */
+ * (bounding_box.rs:69-73).  `cam` may be NULL (the BVH does not depend on the camera).
+ * flags (never change a result, only what gets culled):
+ *   OM_FREEZE_NO_ALWAYS_LIST  scene-sized objects go into the BVH too
+ *   OM_FREEZE_RAY_PADDING / OM_FREEZE_STATIC_PADDING  force / forbid per-ray box padding: the
+ *     margin that makes the boxes cover the reference's f32 round-off grows with the distance
+ *     from the ray origin; scenes of tiny objects spread over a large extent traverse several
+ *     times fewer nodes when it is applied per ray instead of baked in for the worst case.
+ *     Default: chosen from the scene.                                                            */
+#define OM_FREEZE_NO_ALWAYS_LIST (1u << 0)
+#define OM_FREEZE_RAY_PADDING    (1u << 1)
+#define OM_FREEZE_STATIC_PADDING (1u << 2)
 OM_API om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags);
 /* statistics of the frozen scene: [0] bvh nodes, [1] bvh depth, [2] primitives in the BVH,
  * [3] primitives kept in the always-test list, [4] bytes of the device scene image,
- * [5] 1 if the hot part of that image fits in shared memory, [6] cells of the marched-object candidate grid
+ * [5] bit 0: the hot part of that image fits in shared memory, bit 1: per-ray box padding is on
+ * (OM_FREEZE_RAY_PADDING), [6] cells of the marched-object candidate grid
  * (0 = no grid), [7] entries in its lists (rounded up to 4) */
 OM_API om_status om_scene_stats(const om_scene* s, uint64_t stats[8]);
 
@@ -257,7 +268,10 @@ OM_API om_status om_render_samples_done(om_render* r, uint64_t* credited);
 OM_API om_status om_render_samples_traced(om_render* r, uint64_t* traced);
 /* all 16 device counters: [0] credited [1] traced [2] (internal) [3] segments [4] BVH node visits
  * [5] primitive tests [6] SDF evaluations [7] march steps [8] normal evaluations
- * [9] segments that entered the march loop.  [3..9] need OM_RENDER_COUNTERS.  Synchronises.  */
+ * [9] segments that entered the march loop.  [3..9] need OM_RENDER_COUNTERS.
+ * Host side: [10] kernels launched by om_render_launch since create, [11] the flags in force
+ * (with OM_RENDER_WAVEFRONT or OM_RENDER_PERSISTENT as chosen when the caller set neither),
+ * [12] 1 if that pipeline keeps the scene image in shared memory.  Synchronises.              */
 OM_API om_status om_render_perf_counters(om_render* r, uint64_t out[16]);
 /* device time of the launches since the last call to this function, in ms (CUDA events on the
  * render stream).  Synchronises.                                                              */

@@ -252,7 +252,10 @@ class FrozenHittableList:
     def stats(self):
         s = (C.c_uint64 * 8)()
         _lib.call("om_scene_stats", self.h, s)
-        return dict(zip(["bvh_nodes", "bvh_depth", "bvh_prims", "always_test", "device_bytes", "fits_smem", "mgrid_cells", "mgrid_entries"], s))
+        d = dict(zip(["bvh_nodes", "bvh_depth", "bvh_prims", "always_test", "device_bytes", "fits_smem", "mgrid_cells", "mgrid_entries"], s))
+        d["ray_padding"] = (d["fits_smem"] >> 1) & 1
+        d["fits_smem"] &= 1
+        return d
 
     def hit(self, origins, dirs, t_min=0.001, t_max=100.0, flags=0, device=-1):
         """FrozenHittableList::hit (hits.rs:270-334) for a batch of rays -> (obj_id, t, point, normal)."""
@@ -308,7 +311,8 @@ class Renderer:
 
     def perf_counters(self):
         v = (C.c_uint64 * 16)(); _lib.call("om_render_perf_counters", self.h, v)
-        names = ["credited", "traced", "_ticket", "segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals", "march_entered"]
+        names = ["credited", "traced", "_ticket", "segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals", "march_entered",
+                 "kernels", "flags", "scene_in_smem"]
         return dict(zip(names, v))
 
     def elapsed_ms(self):

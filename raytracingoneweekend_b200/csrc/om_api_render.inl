@@ -231,6 +231,7 @@ struct om_render {
     std::vector<EventPair> pending, pool;
     float acc_ms = 0.f;
     uint32_t launches = 0;
+    uint64_t kernels = 0;         // kernels launched by om_render_launch since create (om_render_perf_counters [10])
     bool use_smem = false;       // k_render: scene image in shared memory (one 1024-thread CTA per SM)
     bool use_smem_hook = false;  // parity-hook kernels (two 256-thread CTAs per SM)
     size_t smem_bytes = 0;
@@ -382,8 +383,10 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
         // launch shape: persistent grid of one CTA per SM, hot image in shared memory when it fits
         const bool exact = (p.flags & OM_RENDER_FAST_MATH) == 0, count = (p.flags & OM_RENDER_COUNTERS) != 0;
         const size_t hot_bytes = size_t(r->scene->fz.hdr.hot_units) * 16u;
-        r->use_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 2048u <= r->props.smem_optin;
-        r->use_smem_hook = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= r->props.smem_optin / 2;
+        // (per-ray box padding lives in the global-memory variants only, see node_slab)
+        const bool may_stage = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && r->scene->fz.hdr.dyn_pad == 0.f;
+        r->use_smem = may_stage && hot_bytes + 2048u <= r->props.smem_optin;
+        r->use_smem_hook = may_stage && hot_bytes + 1024u <= r->props.smem_optin / 2;
         r->smem_bytes = hot_bytes;  // each launch wrapper uses it only when its kernel keeps the scene in shared memory
         int occ = exact ? om_exact::render_occupancy(r->use_smem, count, r->smem_bytes) : om_fast::render_occupancy(r->use_smem, count, r->smem_bytes);
         if (occ < 1) {
@@ -408,7 +411,7 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             w.n_slots = n_slots;
             CU(cudaMallocHost(&r->wf_host_ctr, 2 * omk::wf::G_WORDS * 4));
             for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&r->wf_ev[i], cudaEventDisableTiming));
-            r->wf_smem = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + om_exact::wf_stage_bytes() + 1024u <= r->props.smem_optin / 2;
+            r->wf_smem = may_stage && hot_bytes + om_exact::wf_stage_bytes() + 1024u <= r->props.smem_optin / 2;
             int o2 = exact ? om_exact::wf_extend_occupancy(r->wf_smem, count, r->wf_smem ? hot_bytes : 0) : om_fast::wf_extend_occupancy(r->wf_smem, count, r->wf_smem ? hot_bytes : 0);
             if (o2 < 1) return fail(OM_ERR_CUDA, "wavefront extend kernel cannot be resident on device %d", dev);
             r->wf_grid_extend = o2 * r->props.sms;
@@ -459,6 +462,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     cudaError_t e = exact ? om_exact::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream) : om_fast::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream);
     if (e == cudaSuccess) e = om_exact::launch_wf_compact(w, r->wf_grid_small, r->stream);
     if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_wf_shade(init) launch failed: %s", cudaGetErrorString(e));
+    r->kernels += 2;
     w.init = 0;
     const uint32_t BATCH = 16, TAIL = 24576;
     // OM_WF_TIMING=1 (development): device time of each kernel of iterations 8..39, printed to stderr
@@ -491,6 +495,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
             if (e == cudaSuccess) e = om_exact::launch_wf_compact(w, r->wf_grid_small, r->stream);
             if (timing && it >= 8 && it < 8 + TIMED) CU(cudaEventRecord(tev[4 * (it - 8) + 3], r->stream));
             if (e != cudaSuccess) return fail(OM_ERR_CUDA, "wavefront launch failed: %s", cudaGetErrorString(e));
+            r->kernels += 3;
         }
         // snapshot: the rays of iteration `it` are counted in set it % 3
         uint32_t* h = r->wf_host_ctr + slot * omk::wf::G_WORDS;
@@ -519,6 +524,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     a.n_target = n_target;
     e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream) : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
     if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_render (tail) launch failed: %s", cudaGetErrorString(e));
+    r->kernels++;
     return OM_OK;
 }
 }  // namespace
@@ -544,12 +550,14 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
         cudaError_t e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
                               : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
         if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
+        r->kernels++;
     }
     r->n_uniform = n_target;
     if (adaptive) {  // next pass walks only the pixels that still want samples
         CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
         k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, r->live_list, r->live_count);
         CU(cudaGetLastError());
+        r->kernels++;
         r->have_live = true;
     }
     CU(cudaEventRecord(ev.b, r->stream));
@@ -580,6 +588,9 @@ om_status om_render_perf_counters(om_render* r, uint64_t out[16]) {
     CU(cudaSetDevice(r->dev));
     CU(cudaMemcpyAsync(out, r->counters, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, r->stream));
     CU(cudaStreamSynchronize(r->stream));
+    out[10] = r->kernels;
+    out[11] = r->p.flags;  // with the pipeline that was chosen when the caller left it open
+    out[12] = (r->p.flags & OM_RENDER_WAVEFRONT) ? (r->wf_smem ? 1 : 0) : (r->use_smem ? 1 : 0);
     return OM_OK;
 }
 om_status om_render_elapsed_ms(om_render* r, float* ms, uint32_t* launches) {
@@ -746,7 +757,7 @@ om_status om_trace_rays(const om_scene* frozen, const float* origins, const floa
     if (e == cudaSuccess) e = cudaMemcpy(d_d, dirs, b_rays, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "om_trace_rays: upload failed: %s", cudaGetErrorString(e)));
     const size_t hot_bytes = size_t(frozen->fz.hdr.hot_units) * 16u;
-    const bool smem = !(flags & OM_RENDER_NO_SMEM_SCENE) && hot_bytes + 1024u <= props.smem_optin / 2;
+    const bool smem = !(flags & OM_RENDER_NO_SMEM_SCENE) && frozen->fz.hdr.dyn_pad == 0.f && hot_bytes + 1024u <= props.smem_optin / 2;
     const int grid = std::min(ublocks(n), props.sms * 8);
     e = !(flags & OM_RENDER_FAST_MATH) ? om_exact::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0) : om_fast::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();

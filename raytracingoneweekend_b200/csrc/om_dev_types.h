@@ -54,6 +54,9 @@ struct SceneHeader {
     // cold image: cells = uint2 {first, count} (2 per unit) at off_mgrid_cells, lists = j (4 per unit) at off_mgrid_lists
     float mgrid_lo[3], mgrid_inv_h;
     uint32_t mgrid_dim[3], off_mgrid_cells, off_mgrid_lists;
+    // != 0: the BVH boxes carry only the distance-independent padding; the traversal widens each box by
+    // dyn_pad * (largest distance from the ray origin to a point of the box), see om_scene.cpp
+    float dyn_pad;
     uint32_t off_sph_mat;  // hot image: one byte per sphere = its material type (shade class of a hit, om_wavefront.cuh)
 };
 

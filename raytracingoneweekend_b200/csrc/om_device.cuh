@@ -283,6 +283,26 @@ __device__ __forceinline__ float slab(float lx, float ly, float lz, float hx, fl
     return tn <= tf ? tn : kInf;
 }
 
+// Same test against the box widened on every side by pad * D, D = distance from the ray origin to the farthest
+// corner (SceneHeader::dyn_pad): the margin for the reference's round-off, which grows with that distance.
+__device__ __forceinline__ float slab_padded(float lx, float ly, float lz, float hx, float hy, float hz, const RayInv& q, V3 o, float pad, float t_min, float t_max) {
+    const float dx = fmaxf(fabsf(lx - o.x), fabsf(hx - o.x)), dy = fmaxf(fabsf(ly - o.y), fabsf(hy - o.y)), dz = fmaxf(fabsf(lz - o.z), fabsf(hz - o.z));
+    const float e = pad * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+    const float ex = e * fabsf(q.inv.x), ey = e * fabsf(q.inv.y), ez = e * fabsf(q.inv.z);
+    const float ax = fmaf(lx, q.inv.x, q.noinv.x), bx = fmaf(hx, q.inv.x, q.noinv.x);
+    const float ay = fmaf(ly, q.inv.y, q.noinv.y), by = fmaf(hy, q.inv.y, q.noinv.y);
+    const float az = fmaf(lz, q.inv.z, q.noinv.z), bz = fmaf(hz, q.inv.z, q.noinv.z);
+    const float tn = fmaxf(fmaxf(fminf(ax, bx) - ex, fminf(ay, by) - ey), fmaxf(fminf(az, bz) - ez, t_min));
+    const float tf = fminf(fminf(fmaxf(ax, bx) + ex, fmaxf(ay, by) + ey), fminf(fmaxf(az, bz) + ez, t_max));
+    return tn <= tf ? tn : kInf;
+}
+// one BVH child box; the per-ray padding exists only in the global-memory variant (the host never stages such a scene)
+template <bool SMEM>
+__device__ __forceinline__ float node_slab(float lx, float ly, float lz, float hx, float hy, float hz, const RayInv& q, V3 o, float pad, float t_min, float t_max) {
+    if (!SMEM && pad != 0.f) return slab_padded(lx, ly, lz, hx, hy, hz, q, o, pad, t_min, t_max);
+    return slab(lx, ly, lz, hx, hy, hz, q, t_min, t_max);
+}
+
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int STACK_DEPTH = 64;
 
@@ -317,6 +337,7 @@ __device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, c
     const uint32_t n_lin = brute ? (S.n[0] + S.n[1] + S.n[2] + S.n[3] + S.n[4]) : S.n_large;
     const bool have_bvh = !brute && S.n_nodes > 0u;
     const RayInv q = ray_inv(r);
+    const float pad = S.dyn_pad;
     uint32_t k = 0;
     int sp = 0, cur = 0;
     bool act = alive, in_bvh = false;
@@ -344,8 +365,8 @@ __device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, c
                 const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
                 const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
                 if (COUNT) cn.node_visits++;
-                const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, t_min, best.t);
-                const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, t_min, best.t);
+                const float tl = node_slab<SMEM>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, r.o, pad, t_min, best.t);
+                const float tr = node_slab<SMEM>(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, r.o, pad, t_min, best.t);
                 const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                 if (tl < kInf && tr < kInf) {
                     const bool right_first = tr < tl;

@@ -39,10 +39,14 @@ double col_norm_min(const float* m) {  // smallest scale factor of the linear pa
 // away sits at |o_l| = rho = reach / scale radii: `c = |o_l|^2 - 1` and `half_b^2 - a*c` then carry
 // an absolute f32 error of order rho^2 * 2^-23 against the "1", i.e. the test accepts rays that pass
 // within sqrt(1 + k*rho^2*2^-24) radii.  The box must contain that fattened sphere.
+constexpr double kSphereK = 32.0 * 5.96e-8;
+double sphere_fat(const om_sphere& s, double reach) {
+    const double rho = reach / col_norm_min(s.m_local_to_world);
+    return std::sqrt(1.0 + kSphereK * rho * rho) - 1.0;
+}
 Aabb sphere_box(const om_sphere& s, double reach) {
     const float* m = s.m_local_to_world;
-    const double rho = reach / col_norm_min(m);
-    const double fat = std::sqrt(1.0 + 32.0 * 5.96e-8 * rho * rho) - 1.0;
+    const double fat = sphere_fat(s, reach);
     double lo[3], hi[3], extra[3];
     for (int i = 0; i < 3; i++) {
         const double h = std::sqrt(double(m[4 * i]) * m[4 * i] + double(m[4 * i + 1]) * m[4 * i + 1] + double(m[4 * i + 2]) * m[4 * i + 2]);
@@ -55,10 +59,11 @@ Aabb sphere_box(const om_sphere& s, double reach) {
 // traced.rs:301-304 uses +-1; the cube really spans +-0.5 (traced.rs:273-274).  A hit is accepted
 // when the computed local point is within 1e-5 of the surface (traced.rs:284); the computed point
 // itself is off by about rho * 2^-22 local units.
+constexpr double kCubeSlope = 1e-6, kBarySlope = 4e-6;
 Aabb cube_box(const om_cube& s, double reach) {
     const float* m = s.m_local_to_world;
     const double rho = reach / col_norm_min(m);
-    const double fat = 2e-5 + rho * 1e-6;
+    const double fat = 2e-5 + rho * kCubeSlope;
     double lo[3], hi[3], extra[3];
     for (int i = 0; i < 3; i++) {
         const double h = 0.5 * (std::fabs(double(m[4 * i])) + std::fabs(double(m[4 * i + 1])) + std::fabs(double(m[4 * i + 2])));
@@ -77,9 +82,19 @@ Aabb bary_box(const om_barycentric& b, bool parallelogram, double reach) {
         lo[i] = std::min(o, std::min(pu, pv));
         hi[i] = std::max(o, std::max(pu, pv));
         if (parallelogram) { const double puv = pu + double(b.v[i]) * b.v_length; lo[i] = std::min(lo[i], puv); hi[i] = std::max(hi[i], puv); }
-        extra[i] = reach * 4e-6;
+        extra[i] = reach * kBarySlope;
     }
     return padded(lo, hi, extra);
+}
+// Distance-proportional padding.  Each margin above that depends on `reach` is at most slope * D, D = distance from
+// the ray origin to the object's centre (sphere: r*(sqrt(1+K*(D/r)^2)-1) <= sqrt(K)*D; cube and triangle: linear in D
+// by construction), times the object's anisotropy (largest world half extent / smallest scale).  A traversal that
+// widens every box by slope * (largest distance from the ray origin to a point of the box) therefore keeps every
+// candidate a box built with the scene-wide `reach` would keep, and far fewer when the objects are small against it.
+double aniso(const float* m) {
+    double hmax = 0.0;
+    for (int i = 0; i < 3; i++) hmax = std::max(hmax, std::sqrt(double(m[4 * i]) * m[4 * i] + double(m[4 * i + 1]) * m[4 * i + 1] + double(m[4 * i + 2]) * m[4 * i + 2]));
+    return std::max(1.0, hmax / col_norm_min(m));
 }
 double half_area(const Aabb& b) {
     const double dx = double(b.hi[0]) - b.lo[0], dy = double(b.hi[1]) - b.lo[1], dz = double(b.hi[2]) - b.lo[2];
@@ -276,6 +291,25 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
             if (std::isfinite(diag)) reach = std::max(reach, diag);
         }
     }
+    // Static padding is fine while it stays a small share of the objects' own size; when the typical sphere's box
+    // would at least double (tiny spheres in a huge scene), switch to boxes without the distance-dependent part and
+    // let the traversal add it per ray (SceneHeader::dyn_pad).
+    bool dyn = (flags & 2u) != 0;
+    if (!(flags & 6u) && L.spheres.size() >= 64) {
+        std::vector<double> fat;
+        for (const om_sphere& o : L.spheres) fat.push_back(sphere_fat(o, reach));
+        std::nth_element(fat.begin(), fat.begin() + fat.size() / 2, fat.end());
+        dyn = fat[fat.size() / 2] > 0.5;
+    }
+    if (dyn) {
+        double slope = 0.0;
+        for (const om_sphere& o : L.spheres) slope = std::max(slope, std::sqrt(kSphereK) * aniso(o.m_local_to_world));
+        for (const om_cube& o : L.cubes) slope = std::max(slope, 2.0 * kCubeSlope * aniso(o.m_local_to_world));
+        if (!L.triangles.empty() || !L.parallelograms.empty()) slope = std::max(slope, kBarySlope);
+        h.dyn_pad = float(slope * 1.01);
+        if (!(h.dyn_pad > 0.f) || !std::isfinite(h.dyn_pad)) { dyn = false; h.dyn_pad = 0.f; }
+    }
+    if (dyn) reach = 0.0;
     std::vector<uint32_t> refs;
     std::vector<Aabb> boxes;
     for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i], reach)); }

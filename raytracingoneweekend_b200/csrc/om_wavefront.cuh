@@ -191,8 +191,8 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 2) k_wf_extend(const __grid_co
                     const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
                     const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
                     if (COUNT) cn.node_visits++;
-                    const float tl = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, A.tmin, best.t);
-                    const float tr = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, A.tmin, best.t);
+                    const float tl = node_slab<SMEM>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, ray.o, S.dyn_pad, A.tmin, best.t);
+                    const float tr = node_slab<SMEM>(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, ray.o, S.dyn_pad, A.tmin, best.t);
                     const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                     if (tl < kInf && tr < kInf) {
                         const bool right_first = tr < tl;

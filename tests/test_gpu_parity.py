@@ -1,6 +1,7 @@
 """GPU parity tests: the CUDA path, called through the C ABI, against the oracle on the same
 seeded inputs.  Default build (the reference's arithmetic, FMA only in culling): bit-exact.
 OM_RENDER_FAST_MATH build: tolerances stated in each test."""
+import ctypes
 import os
 
 import numpy as np
@@ -131,6 +132,35 @@ def test_hit_bit_exact_many_spheres_global_bvh(api, A, O):
     o = np.tile(np.array([60, 12, 14], np.float32), (4000, 1))
     tgt = rng.uniform(-40, 40, (4000, 3)).astype(np.float32); tgt[:, 1] = rng.uniform(0, 4, 4000)
     assert_hits_equal(fz.hit(o, tgt - o, 0.001, 1000.0, flags=0), osc.trace_rays(o, tgt - o, 0.001, 1000.0))
+
+
+@pytest.mark.parametrize("freeze_flags", [0, 2, 4])  # chosen from the scene / per-ray box padding / worst-case static padding
+def test_hit_bit_exact_ill_conditioned_tiny_spheres(api, A, O, freeze_flags):
+    """Sphere::hit (traced.rs:38-56) from an origin thousands of radii away rounds `|o_l|^2 - 1` and the discriminant so
+    coarsely that rays passing well outside a sphere are reported as hits; the culling has to keep every one of them."""
+    fz = api.FrozenHittableList.generate("many_spheres", 5, 20000, flags=freeze_flags)
+    st = fz.stats()
+    assert st["ray_padding"] == (0 if freeze_flags == 4 else 1)
+    osc = oracle_scene_from(O, fz)
+    sph = np.frombuffer(fz.lists()["spheres"], dtype=np.float32).reshape(-1, ctypes.sizeof(A.Sphere) // 4)
+    ctr = sph[1:, [3, 7, 11]]  # (sphere 0 is the ground)
+    rad = np.abs(sph[1:, 0])
+    rng = np.random.default_rng(9)
+    n = 6000
+    pick = rng.integers(0, ctr.shape[0], n)
+    u = rng.normal(size=(n, 3)); u /= np.linalg.norm(u, axis=1, keepdims=True); u[:, 1] = np.abs(u[:, 1]) + 0.05
+    v = np.cross(u, rng.normal(size=(n, 3))); v /= np.linalg.norm(v, axis=1, keepdims=True)
+    dist = rng.uniform(150, 420, (n, 1))
+    miss = rng.uniform(0.2, 5.0, (n, 1))  # impact parameter in radii
+    o = (ctr[pick] + u * dist).astype(np.float32)
+    tgt = ctr[pick] + v * miss * rad[pick, None]
+    d = ((tgt - o) / dist * rng.uniform(0.5, 2.0, (n, 1))).astype(np.float32)
+    want = osc.trace_rays(o, d, 0.001, 1000.0)
+    assert_hits_equal(fz.hit(o, d, 0.001, 1000.0, flags=0), want)
+    assert_hits_equal(fz.hit(o, d, 0.001, 1000.0, flags=A.RENDER_BRUTE_FORCE), want)
+    # the case is really exercised: the aimed-at sphere is reported hit by rays that geometrically pass outside it
+    aimed = want[0] == ((np.uint64(1) << np.uint64(32)) | (pick + 2).astype(np.uint64))  # OM_OBJ_ID(sphere, 1 + pick)
+    assert (aimed & (miss[:, 0] > 1.5)).sum() > 20
 
 
 def test_fast_math_build_hit_tolerance(api, A, rtiow, O):
