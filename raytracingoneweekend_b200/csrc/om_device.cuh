@@ -36,6 +36,9 @@ constexpr int CTA_THREADS = 256;
 #define OM_RENDER_THREADS 1024  // one CTA per SM: one copy of the scene image, 32 warps (64 registers) to hide the
 #define OM_RENDER_MIN_CTAS 1    // instruction-cache misses of this 70 KB kernel: +23 % over 2 x 256 threads at 92 registers
 #endif
+#ifndef OM_PHASE_SYNC
+#define OM_PHASE_SYNC 0  // experiment: CTA-wide barriers between the traversal and the shading phase of k_render
+#endif
 constexpr int RENDER_THREADS = OM_RENDER_THREADS;  // k_render only
 
 using omk::RenderArgs;
@@ -881,6 +884,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         bool fresh = true;
         while (__any_sync(FULL, todo > 0u)) {
             const bool alive = todo > 0u;
+#if OM_PHASE_SYNC
+            __syncthreads_count(1);
+#endif
             if (alive && fresh) {
                 const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
                 rng_init(g, A.seed_lo, A.seed_hi, pxl, sample);
@@ -890,6 +896,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
                 fresh = false;
             }
             Hit h = closest_hit_warp<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
+#if OM_PHASE_SYNC > 1
+            __syncthreads();
+#endif
             if (alive) {
                 bool finished;
                 V3 result = color;
@@ -926,6 +935,14 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         }
     }
 
+#if OM_PHASE_SYNC
+    // out of tickets: keep answering the phase barriers until every warp of the CTA is out
+    while (__syncthreads_count(0) > 0) {
+#if OM_PHASE_SYNC > 1
+        __syncthreads();
+#endif
+    }
+#endif
     // ---- progress counters: warp-aggregate, one atomic per warp ----
     for (int o = 16; o > 0; o >>= 1) {
         credited += __shfl_xor_sync(FULL, credited, o);
