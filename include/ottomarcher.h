@@ -177,7 +177,8 @@ enum {
     /* force the persistent path-regeneration kernel.  With neither this nor OM_RENDER_WAVEFRONT the
      * library picks: wavefront when the scene image does not fit in shared memory (the BVH is then
      * walked through L2, which wants many more rays in flight) or when it has more than 8 marched
-     * objects (long SDF marches stall the persistent kernel's warps); persistent kernel otherwise. */
+     * objects and no distance BVH over them (OM_FREEZE_NO_MARCHED_BVH; full-scan SDF marches stall
+     * the persistent kernel's warps); persistent kernel otherwise.                                */
     OM_RENDER_PERSISTENT = 1u << 6
 };
 
@@ -241,6 +242,8 @@ OM_API om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out,
 #define OM_FREEZE_NO_ALWAYS_LIST (1u << 0)
 #define OM_FREEZE_RAY_PADDING    (1u << 1)
 #define OM_FREEZE_STATIC_PADDING (1u << 2)
+/* no distance BVH over the marched objects (min_j |sdf_j| by the full scan outside the candidate grid) */
+#define OM_FREEZE_NO_MARCHED_BVH (1u << 3)
 OM_API om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags);
 /* statistics of the frozen scene: [0] bvh nodes, [1] bvh depth, [2] primitives in the BVH,
  * [3] primitives kept in the always-test list, [4] bytes of the device scene image,

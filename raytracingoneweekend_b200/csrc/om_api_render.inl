@@ -396,7 +396,9 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
         r->grid = occ * r->props.sms;
         if (!(p.flags & (OM_RENDER_WAVEFRONT | OM_RENDER_PERSISTENT))) {  // automatic choice (see OM_RENDER_PERSISTENT)
             const bool fits = hot_bytes + om_exact::wf_stage_bytes() + 1024u <= r->props.smem_optin / 2;
-            if (!fits || r->scene->fz.hdr.n_marched > 8u) r->p.flags |= OM_RENDER_WAVEFRONT;
+            // many marched objects without a distance BVH: long SDF loops stall the persistent kernel's warps
+            const bool slow_march = r->scene->fz.hdr.n_marched > 8u && r->scene->fz.hdr.n_mbvh_nodes == 0u;
+            if (!fits || slow_march) r->p.flags |= OM_RENDER_WAVEFRONT;
         }
         if (r->p.flags & OM_RENDER_WAVEFRONT) {
             // slot pool: resident in L2 (72 B of path state per slot), never more slots than pixels

@@ -54,6 +54,11 @@ struct SceneHeader {
     // cold image: cells = uint2 {first, count} (2 per unit) at off_mgrid_cells, lists = j (4 per unit) at off_mgrid_lists
     float mgrid_lo[3], mgrid_inv_h;
     uint32_t mgrid_dim[3], off_mgrid_cells, off_mgrid_lists;
+    // Distance BVH over the marched objects (0 nodes = none), used where the grid does not reach: nodes as in the traced
+    // BVH (64 B, both children's boxes, child < 0 = ~j) at off_mbvh_nodes in the cold image; objects too large to bound
+    // usefully (j, 4 per unit) at off_mbvh_always.  |sdf_j(p)| >= mbvh_f * dist(p, box_j) - mbvh_margin * (1 + |p|).
+    uint32_t n_mbvh_nodes, off_mbvh_nodes, n_mbvh_always, off_mbvh_always;
+    float mbvh_f, mbvh_margin;
     // != 0: the BVH boxes carry only the distance-independent padding; the traversal widens each box by
     // dyn_pad * (largest distance from the ray origin to a point of the box), see om_scene.cpp
     float dyn_pad;

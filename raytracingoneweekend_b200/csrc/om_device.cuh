@@ -471,20 +471,34 @@ __device__ __forceinline__ uint32_t marched_ref(const SceneHeader& S, uint32_t j
     if (j < n_ms + n_mb) return omd::make_ref(omd::PT_MBOX, j - n_ms);
     return omd::make_ref(omd::PT_MTORUS, j - n_ms - n_mb);
 }
+constexpr int MSTACK = 40;  // scratch entries nearest_marched needs (<= STACK_DEPTH: the traversal stack is free by then)
 struct Near {
     uint32_t evals;  // SDFs evaluated (executed-work accounting)
     float d;       // min over the marched objects of |sdf(p)|
     uint32_t ref;  // the first object that attains it (strict `<`, hits.rs:304,345); REF_NONE if none
 };
 template <bool SMEM>
-__device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p) {
+__device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p);
+// min_j |sdf_j(p)| with help of the host-built structures (scenes with many marched objects):
+//  - inside the candidate grid only the cell's list is evaluated, in the reference's order: the objects left out are
+//    provably farther than a listed one everywhere in the cell (om_scene.cpp, build_marched_grid);
+//  - elsewhere the distance BVH is walked with the exact minimum found so far as the bound.  A subtree is skipped only when
+//    a LOWER bound of every |sdf| in it is strictly above that minimum, so what is skipped can neither be the minimum nor
+//    tie with it; the tree hands objects out of order, so an equal value from a smaller index takes over — the first
+//    object of the reference's scan that attains the minimum (om_scene.cpp, build_marched_bvh).
+// When the walk runs out of scratch stack it scans every object instead.
+template <bool SMEM>
+__device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const SceneHeader& S, V3 p, int2* stk) {
     Near n;
     n.d = kInf;
     n.ref = omd::REF_NONE;
-    n.evals = S.n_marched;
+    n.evals = 0;
+    auto word = [&](uint32_t off, uint32_t i) {
+        const float4 l4 = sv.cold(off + (i >> 2));
+        const uint32_t sel = i & 3u;
+        return __float_as_uint(sel == 0u ? l4.x : (sel == 1u ? l4.y : (sel == 2u ? l4.z : l4.w)));
+    };
     if (S.mgrid_dim[0] != 0u) {
-        // inside the candidate grid only the cell's list is evaluated, in the same order: the objects left out are
-        // provably farther than a listed one everywhere in the cell (om_scene.cpp, build_marched_grid)
         const float fx = (p.x - S.mgrid_lo[0]) * S.mgrid_inv_h, fy = (p.y - S.mgrid_lo[1]) * S.mgrid_inv_h, fz = (p.z - S.mgrid_lo[2]) * S.mgrid_inv_h;
         if (fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < (float)S.mgrid_dim[0] && fy < (float)S.mgrid_dim[1] && fz < (float)S.mgrid_dim[2]) {
             const uint32_t cell = ((uint32_t)fz * S.mgrid_dim[1] + (uint32_t)fy) * S.mgrid_dim[0] + (uint32_t)fx;
@@ -492,22 +506,68 @@ __device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHead
             const uint32_t first = __float_as_uint((cell & 1u) ? cc.z : cc.x), count = __float_as_uint((cell & 1u) ? cc.w : cc.y);
             n.evals = count;
             for (uint32_t k = first; k < first + count; k++) {
-                const float4 l4 = sv.cold(S.off_mgrid_lists + (k >> 2));
-                const uint32_t sel = k & 3u;
-                const uint32_t j = __float_as_uint(sel == 0u ? l4.x : (sel == 1u ? l4.y : (sel == 2u ? l4.z : l4.w)));
-                const uint32_t ref = marched_ref(S, j);
+                const uint32_t ref = marched_ref(S, word(S.off_mgrid_lists, k));
                 const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
                 if (d < n.d) { n.d = d; n.ref = ref; }
             }
             return n;
         }
     }
+    bool walk = S.n_mbvh_nodes != 0u;
+    const float slack = S.mbvh_margin + 1e-5f * (fabsf(p.x) + fabsf(p.y) + fabsf(p.z));
+    auto lower = [&](float lx, float ly, float lz, float hx, float hy, float hz) {
+        const float dx = fmaxf(fmaxf(lx - p.x, p.x - hx), 0.f), dy = fmaxf(fmaxf(ly - p.y, p.y - hy), 0.f), dz = fmaxf(fmaxf(lz - p.z, p.z - hz), 0.f);
+        return S.mbvh_f * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - slack;
+    };
+    uint32_t k = 0, best_j = 0xFFFFFFFFu;
+    int sp = 1;
+    stk[0] = make_int2(0, __float_as_int(-1.f));  // the root, after the scene-sized objects of the always list
+    while (walk) {
+        uint32_t j = 0xFFFFFFFFu;
+        if (k < S.n_mbvh_always) { j = word(S.off_mbvh_always, k); k++; }
+        else {
+            while (sp > 0) {
+                sp--;
+                const int2 e = stk[sp];
+                if (__int_as_float(e.y) > n.d) continue;
+                if (e.x < 0) { j = (uint32_t)(~e.x); break; }
+                const uint32_t u = S.off_mbvh_nodes + omd::U_NODE * (uint32_t)e.x;
+                const float4 n0 = sv.cold(u), n1 = sv.cold(u + 1), n2 = sv.cold(u + 2), n3 = sv.cold(u + 3);
+                float dl = lower(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y), dr = lower(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w);
+                int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
+                if (dr < dl) { const float t = dl; dl = dr; dr = t; const int c = cl; cl = cr; cr = c; }  // (cl, dl): the nearer child, popped first
+                if (sp + 2 > MSTACK) { walk = false; break; }
+                if (!(dr > n.d)) { stk[sp] = make_int2(cr, __float_as_int(dr)); sp++; }
+                if (!(dl > n.d)) { stk[sp] = make_int2(cl, __float_as_int(dl)); sp++; }
+            }
+        }
+        if (!walk) break;
+        if (j == 0xFFFFFFFFu) return n;
+        const uint32_t ref = marched_ref(S, j);
+        const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+        n.evals++;
+        if (d < n.d || (d == n.d && j < best_j && best_j != 0xFFFFFFFFu)) { n.d = d; n.ref = ref; best_j = j; }
+    }
+    return nearest_marched(sv, S, p);
+}
+template <bool SMEM>
+__device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p) {  // hits.rs:301-311
+    Near n;
+    n.d = kInf;
+    n.ref = omd::REF_NONE;
+    n.evals = S.n_marched;
     for (uint32_t j = 0; j < S.n_marched; j++) {
         const uint32_t ref = marched_ref(S, j);
         const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
         if (d < n.d) { n.d = d; n.ref = ref; }
     }
     return n;
+}
+// The same value through the host-built structures when the scene has them (warp-uniform choice)
+template <bool SMEM>
+__device__ __forceinline__ Near nearest_marched(const SceneView<SMEM>& sv, const SceneHeader& S, V3 p, int2* stk) {  // stk: MSTACK entries of scratch
+    if ((S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u) return nearest_marched_accel(sv, S, p, stk);
+    return nearest_marched(sv, S, p);
 }
 template <bool SMEM>
 __device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& S, uint32_t ref, V3 p) {
@@ -523,8 +583,11 @@ struct Hit {
 // FrozenHittableList::hit, marched part (hits.rs:288-332) + unstuck (hits.rs:336-365).
 // `closest` is the traced hit distance (or t_max).  Returns ref == REF_NONE when the march ends
 // without a hit (the traced record stands).
-template <bool SMEM, bool COUNT>
-__device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, Counters* cn) {
+// ACCEL: the scene has a candidate grid / distance BVH.  k_render is instantiated for either case (template MA) and the host
+// picks: merely linking the structures' code into the kernel that renders C2 (one marched torus, never uses them) cost it
+// 8-10 % (more spill traffic in the 64-register main body), so that kernel does not contain it.
+template <bool SMEM, bool COUNT, bool ACCEL>
+__device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, Counters* cn, int2* stk) {
     Hit out;
     out.t = closest;
     out.ref = omd::REF_NONE;
@@ -536,7 +599,7 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
     {
         const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
         float new_t = t_min;
-        const Near n0 = nearest_marched(sv, S, ray_at(r, t_min));
+        const Near n0 = ACCEL ? nearest_marched_accel(sv, S, ray_at(r, t_min), stk) : nearest_marched(sv, S, ray_at(r, t_min));
         if (COUNT) cn->sdf_evals += n0.evals;
         if (n0.ref == omd::REF_NONE) return out;  // `marched.is_none()` -> INF -> return rec (also every NaN ray)
         float aux = n0.d;
@@ -554,7 +617,7 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
     while (t < t_max && t < closest && max_march_iter > 0) {
         max_march_iter--;
         const V3 point = ray_at(r, t);
-        const Near n = nearest_marched(sv, S, point);
+        const Near n = ACCEL ? nearest_marched_accel(sv, S, point, stk) : nearest_marched(sv, S, point);
         if (COUNT) { cn->march_steps++; cn->sdf_evals += n.evals; }
         if (n.ref == omd::REF_NONE) return out;  // `material.is_none()`
         if (n.d < HIT_SIZE) {
@@ -574,7 +637,8 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
 
 // FrozenHittableList::hit (hits.rs:270-334); also first_hit (the BVH subsumes CameraHash).
 // Warp-collective: all 32 lanes call it, `alive` marks the lanes that carry a ray.
-template <bool SMEM, bool COUNT>
+// MA: 0 = the scene has no candidate grid / distance BVH, 1 = it has, 2 = look at the header (parity hooks)
+template <bool SMEM, bool COUNT, int MA>
 __device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, bool alive,
                                                 Counters& cn, int2* stack) {
     if (COUNT && alive) cn.segments++;
@@ -591,7 +655,13 @@ __device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const
         const RayInv q = ray_inv(r);
         const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, t_min, fminf(t_max, h.t));
         if (te < kInf) {
-            const Hit m = march<SMEM, COUNT>(sv, S, r, t_min, t_max, h.t, &cn);
+            auto run = [&]() -> Hit {
+                if constexpr (MA == 0) return march<SMEM, COUNT, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+                else if constexpr (MA == 1) return march<SMEM, COUNT, true>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+                else return (S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u ? march<SMEM, COUNT, true>(sv, S, r, t_min, t_max, h.t, &cn, stack)
+                                                                   : march<SMEM, COUNT, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+            };
+            const Hit m = run();
             if (m.ref != omd::REF_NONE) h = m;
         }
     }
@@ -829,7 +899,7 @@ __device__ __forceinline__ void stage_scene_smem(const float4* hot_g, uint32_t u
 // never wait for each other's paths; the accumulators live in registers between the single
 // coalesced read and write of the pixel's 32-byte state.
 // ============================================================================================
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool COUNT, int MA>
 __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(const __grid_constant__ RenderArgs A) {
     if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
     SceneView<SMEM> sv;
@@ -895,7 +965,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
                 seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
                 fresh = false;
             }
-            Hit h = closest_hit_warp<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
+            Hit h = closest_hit_warp<SMEM, COUNT, MA>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
 #if OM_PHASE_SYNC > 1
             __syncthreads();
 #endif
@@ -983,7 +1053,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_primary(const __grid_constan
             if (mode == 0u) ray = center_ray(A, pxl);
             else { Rng g; rng_init(g, A.seed_lo, A.seed_hi, pxl, sample_index); ray = primary_ray(A, pxl, sample_index, g); }
         }
-        const Hit h = closest_hit_warp<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
+        const Hit h = closest_hit_warp<SMEM, false, 2>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
         if (alive) {
             if (h.ref == omd::REF_NONE) { ids[pxl] = 0ull; tout[pxl] = kInf; }
             else { ids[pxl] = ((unsigned long long)(omd::ref_type(h.ref) + 1u) << 32) | (unsigned long long)(omd::ref_index(h.ref) + 1u); tout[pxl] = h.t; }
@@ -1009,7 +1079,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_trace_rays(const __grid_cons
             ray.o = v3(A.origins[3 * i], A.origins[3 * i + 1], A.origins[3 * i + 2]);
             ray.d = om::unit(v3(A.dirs[3 * i], A.dirs[3 * i + 1], A.dirs[3 * i + 2]));
         }
-        Hit h = closest_hit_warp<SMEM, false>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
+        Hit h = closest_hit_warp<SMEM, false, 2>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
         if (!alive) continue;
         const bool hit = h.ref != omd::REF_NONE;
         if (hit) finish_hit(sv, A.scene, ray, A.tmin, h);

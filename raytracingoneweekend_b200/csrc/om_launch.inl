@@ -6,28 +6,35 @@ static cudaError_t prep(K kern, size_t smem_bytes) {
     return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
 }
 
-// resident CTAs per SM of the render kernel for this configuration
+// k_render<SMEM, COUNT, MA>: MA = 1 when the scene carries a candidate grid / distance BVH over its marched objects
+template <class F>
+static void with_render_kernel(bool smem, bool count, bool maccel, F f) {
+    if (smem) {
+        if (count) { if (maccel) f(k_render<true, true, 1>); else f(k_render<true, true, 0>); }
+        else { if (maccel) f(k_render<true, false, 1>); else f(k_render<true, false, 0>); }
+    } else {
+        if (count) { if (maccel) f(k_render<false, true, 1>); else f(k_render<false, true, 0>); }
+        else { if (maccel) f(k_render<false, false, 1>); else f(k_render<false, false, 0>); }
+    }
+}
+static bool scene_has_march_accel(const omk::RenderArgs& a) { return (a.scene.mgrid_dim[0] | a.scene.n_mbvh_nodes) != 0u; }
+
+// resident CTAs per SM of the render kernel for this configuration (the same for both MA instances: one launch bound)
 int render_occupancy(bool smem, bool count, size_t smem_bytes) {
     int n = 0;
-    cudaError_t e;
-    if (smem) {
-        if (count) { prep(k_render<true, true>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, true>, RENDER_THREADS, smem_bytes); }
-        else { prep(k_render<true, false>, smem_bytes); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<true, false>, RENDER_THREADS, smem_bytes); }
-    } else {
-        if (count) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, true>, RENDER_THREADS, 0);
-        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render<false, false>, RENDER_THREADS, 0);
-    }
+    cudaError_t e = cudaSuccess;
+    with_render_kernel(smem, count, false, [&](auto kern) {
+        if (smem) prep(kern, smem_bytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, RENDER_THREADS, smem ? smem_bytes : 0);
+    });
     return e == cudaSuccess ? n : 0;
 }
 
 cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st) {
-    if (smem) {
-        if (count) { prep(k_render<true, true>, smem_bytes); k_render<true, true><<<grid, RENDER_THREADS, smem_bytes, st>>>(a); }
-        else { prep(k_render<true, false>, smem_bytes); k_render<true, false><<<grid, RENDER_THREADS, smem_bytes, st>>>(a); }
-    } else {
-        if (count) k_render<false, true><<<grid, RENDER_THREADS, 0, st>>>(a);
-        else k_render<false, false><<<grid, RENDER_THREADS, 0, st>>>(a);
-    }
+    with_render_kernel(smem, count, scene_has_march_accel(a), [&](auto kern) {
+        if (smem) prep(kern, smem_bytes);
+        kern<<<grid, RENDER_THREADS, smem ? smem_bytes : 0, st>>>(a);
+    });
     return cudaGetLastError();
 }
 

@@ -248,6 +248,89 @@ void build_marched_grid(const omh::SceneLists& L, omd::SceneHeader& h, Packer& c
     h.off_mgrid_lists = cold.units();
     for (size_t k = 0; k < lists.size(); k += 4) cold.u4(lists[k], k + 1 < lists.size() ? lists[k + 1] : 0u, k + 2 < lists.size() ? lists[k + 2] : 0u, k + 3 < lists.size() ? lists[k + 3] : 0u);
 }
+
+// ---- distance BVH over the marched objects (see SceneHeader::mbvh_*) ----------------------------------------
+// Every object gets a proxy box B_j and a factor f_j in (0,1] with |sdf_j(p)| >= f_j * dist(p, B_j) for every p:
+//   sphere | |p-c| - r |          >= |p-c| - |r|                >= dist(p, c +- |r|)
+//   box    (marched.rs:86-89)     exact distance outside, |.| >= 0 inside: B = c +- |sizes|
+//   torus  local_sdf(q) * min scale (marched.rs:134-150): exact in local space, and the local->world map stretches
+//          lengths by at most the largest scale, so f = min scale / max scale over a ball around the torus.
+// The device walks the tree with the exact minimum found so far as the pruning bound (nearest_marched).
+void build_marched_bvh(const omh::SceneLists& L, omd::SceneHeader& h, Packer& cold) {
+    const size_t ns = L.marched_spheres.size(), nb = L.marched_boxes.size(), nt = L.marched_tori.size(), n = ns + nb + nt;
+    if (n < 6) return;
+    std::vector<Aabb> box(n);
+    std::vector<double> f(n, 1.0);
+    std::vector<bool> ok(n, true);
+    auto set_box = [&](size_t j, const double c[3], const double r[3]) {
+        for (int a = 0; a < 3; a++) {
+            const double m = 1e-5 * (1 + std::fabs(c[a]) + r[a]);  // proxies err on the large side
+            box[j].lo[a] = nextafterf(float(c[a] - r[a] - m), -kInf); box[j].hi[a] = nextafterf(float(c[a] + r[a] + m), kInf);
+            if (!std::isfinite(box[j].lo[a]) || !std::isfinite(box[j].hi[a])) ok[j] = false;
+        }
+    };
+    for (size_t i = 0; i < ns; i++) {
+        const auto& s = L.marched_spheres[i];
+        const double c[3] = {s.center[0], s.center[1], s.center[2]}, r[3] = {std::fabs(double(s.radius)), std::fabs(double(s.radius)), std::fabs(double(s.radius))};
+        set_box(i, c, r);
+    }
+    for (size_t i = 0; i < nb; i++) {
+        const auto& s = L.marched_boxes[i];
+        const double c[3] = {s.center[0], s.center[1], s.center[2]}, r[3] = {std::fabs(double(s.sizes[0])), std::fabs(double(s.sizes[1])), std::fabs(double(s.sizes[2]))};
+        set_box(ns + i, c, r);
+    }
+    for (size_t i = 0; i < nt; i++) {
+        const auto& s = L.marched_tori[i];
+        const size_t j = ns + nb + i;
+        const float* m = s.m_local_to_world_translate_rotate; const float* sc = s.m_local_to_world_scale;
+        double smin = 1e300, smax = 0;
+        for (int a = 0; a < 3; a++) { smin = std::min(smin, std::fabs(double(sc[a]))); smax = std::max(smax, std::fabs(double(sc[a]))); }
+        // rows of the rotation part should be unit; a sloppy matrix only makes the ball larger
+        double rown = 1.0;
+        for (int r = 0; r < 3; r++) rown = std::max(rown, std::sqrt(double(m[4 * r]) * m[4 * r] + double(m[4 * r + 1]) * m[4 * r + 1] + double(m[4 * r + 2]) * m[4 * r + 2]));
+        const double c[3] = {double(m[3]) * sc[0], double(m[7]) * sc[1], double(m[11]) * sc[2]};
+        const double rad = (std::fabs(double(s.sizes[0])) + std::fabs(double(s.sizes[1]))) * smax * rown * 1.7320508;
+        const double r[3] = {rad, rad, rad};
+        set_box(j, c, r);
+        // value = local_sdf * min_val(l2w scale) (signed min, marched.rs:149); a non-positive or wildly uneven scale is not bounded here
+        const double mv = std::min(double(sc[0]), std::min(double(sc[1]), double(sc[2])));
+        f[j] = (mv > 0 && smax > 0) ? mv / (smax * rown) : 0.0;
+        if (!(f[j] > 1e-3) || !std::isfinite(rad)) ok[j] = false;
+    }
+    // scene-sized or unbounded objects are evaluated at every query (like the traced always-test list)
+    Aabb all;
+    for (int a = 0; a < 3; a++) { all.lo[a] = kInf; all.hi[a] = -kInf; }
+    size_t nok = 0;
+    for (size_t j = 0; j < n; j++) if (ok[j]) { nok++; for (int a = 0; a < 3; a++) { all.lo[a] = std::min(all.lo[a], box[j].lo[a]); all.hi[a] = std::max(all.hi[a], box[j].hi[a]); } }
+    if (nok < 4) return;
+    const double total = half_area(all);
+    std::vector<uint32_t> always, refs;
+    std::vector<Aabb> boxes;
+    double fmin = 1.0, ext = 0.0;
+    for (size_t j = 0; j < n; j++) {
+        if (!ok[j] || (half_area(box[j]) >= 0.25 * total && always.size() < 16)) { always.push_back(uint32_t(j)); continue; }
+        refs.push_back(uint32_t(j)); boxes.push_back(box[j]);
+        fmin = std::min(fmin, f[j]);
+        for (int a = 0; a < 3; a++) ext = std::max(ext, std::max(std::fabs(double(box[j].lo[a])), std::fabs(double(box[j].hi[a]))));
+    }
+    if (refs.size() < 4 || always.size() > 16) return;
+    omb::BuildResult bvh;
+    omb::build(refs, boxes, bvh);
+    if (bvh.nodes.empty() || bvh.depth > 40) return;
+    h.mbvh_f = float(fmin * (1 - 1e-4));
+    h.mbvh_margin = float(1e-5 * (1 + ext));
+    h.n_mbvh_nodes = uint32_t(bvh.nodes.size());
+    h.n_mbvh_always = uint32_t(always.size());
+    h.off_mbvh_always = cold.units();
+    for (size_t k = 0; k < always.size(); k += 4) cold.u4(always[k], k + 1 < always.size() ? always[k + 1] : 0u, k + 2 < always.size() ? always[k + 2] : 0u, k + 3 < always.size() ? always[k + 3] : 0u);
+    h.off_mbvh_nodes = cold.units();
+    for (const omb::Node& nd : bvh.nodes) {
+        cold.f4(nd.lmin[0], nd.lmin[1], nd.lmin[2], nd.lmax[0]);
+        cold.f4(nd.lmax[1], nd.lmax[2], nd.rmin[0], nd.rmin[1]);
+        cold.f4(nd.rmin[2], nd.rmax[0], nd.rmax[1], nd.rmax[2]);
+        cold.u4(uint32_t(nd.left), uint32_t(nd.right), 0u, 0u);
+    }
+}
 }  // namespace
 
 void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, FrozenScene& out) {
@@ -442,6 +525,7 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
     mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
     mats(PT_PARA, L.parallelograms); mats(PT_MSPHERE, L.marched_spheres); mats(PT_MBOX, L.marched_boxes); mats(PT_MTORUS, L.marched_tori);
     build_marched_grid(L, h, cold);
+    if (!(flags & 8u)) build_marched_bvh(L, h, cold);
     if (cold.units() == 0) cold.f4(0, 0, 0, 0);
     if (hot.units() == 0) hot.f4(0, 0, 0, 0);
     h.hot_units = hot.units();

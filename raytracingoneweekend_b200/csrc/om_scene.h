@@ -17,6 +17,7 @@ struct FrozenScene {
 
 // flags: bit 0 = put every bounded primitive in the BVH even when it is scene-sized;
 //        bit 1 / bit 2 = force / forbid per-ray box padding (SceneHeader::dyn_pad; default: chosen from the scene)
+//        bit 3 = no distance BVH over the marched objects (SceneHeader::mbvh_*)
 // cam (may be NULL) only widens the numerical margins of the boxes; it never changes a result.
 void freeze(const omh::SceneLists& lists, const om_camera* cam, uint32_t flags, FrozenScene& out);
 

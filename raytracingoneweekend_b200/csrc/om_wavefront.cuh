@@ -247,6 +247,7 @@ __device__ __noinline__ void wf_march_warp(const RenderArgs& A, const omk::WfArg
     uint32_t* ns = wf_set(W, W.it + 1u);
     const int steps = (int)min(64u, max(8u, 512u / S.n_marched));
     uint32_t dest = WF_NONE, slot = 0;
+    int2 mstk[MSTACK];  // scratch of nearest_marched's distance-BVH walk
     if (i < n) {
         slot = W.q_march[W.it & 1u][i];
         const float4 o = W.s_ray[2u * slot], d = W.s_ray[2u * slot + 1u];
@@ -263,7 +264,7 @@ __device__ __noinline__ void wf_march_warp(const RenderArgs& A, const omk::WfArg
         int budget = steps;
         uint32_t code = __float_as_uint(hm.w);
         if (code == WF_NONE) {
-            const Near n0 = nearest_marched(sv, S, ray_at(ray, A.tmin));
+            const Near n0 = nearest_marched(sv, S, ray_at(ray, A.tmin), mstk);
             if (COUNT) { cn.march_entered++; cn.sdf_evals += n0.evals; }
             if (n0.ref == omd::REF_NONE) finished = true;  // `marched.is_none()` -> INF -> return rec (also every NaN ray)
             else if (n0.d < HIT_SIZE) { code = 0x80000000u | n0.ref; t_m = A.tmin; }
@@ -291,7 +292,7 @@ __device__ __noinline__ void wf_march_warp(const RenderArgs& A, const omk::WfArg
             for (; budget > 0; budget--) {  // hits.rs:294-332
                 if (!(t_m < A.tmax && t_m < closest && iter > 0)) { finished = true; break; }
                 iter--;
-                const Near nn = nearest_marched(sv, S, ray_at(ray, t_m));
+                const Near nn = nearest_marched(sv, S, ray_at(ray, t_m), mstk);
                 if (COUNT) { cn.march_steps++; cn.sdf_evals += nn.evals; }
                 if (nn.ref == omd::REF_NONE) { finished = true; break; }  // `material.is_none()`
                 if (nn.d < HIT_SIZE) {

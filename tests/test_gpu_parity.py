@@ -398,3 +398,34 @@ def test_marched_candidate_grid_hit_bit_exact(api, A, O):
     d2 = rng.normal(0, 1, (6000, 3)).astype(np.float32)
     assert_hits_equal(fz.hit(o2, d2), osc.trace_rays(o2, d2))
     assert_hits_equal(fz.hit(o2, d2, flags=A.RENDER_NO_SMEM_SCENE), osc.trace_rays(o2, d2))
+
+
+@pytest.mark.parametrize("freeze_flags", [0, 8])  # with / without the distance BVH over the marched objects
+def test_marched_distance_bvh_hit_bit_exact(api, A, O, freeze_flags):
+    """Outside the candidate grid min_j |sdf_j| comes from a BVH walk bounded by the exact minimum so far
+    (nearest_marched); rays that start or travel far from the objects must give the full loop's ids, t, points, normals."""
+    fz = api.FrozenHittableList.generate("marched", 3, flags=freeze_flags)
+    osc = oracle_scene_from(O, fz)
+    rng = np.random.default_rng(16)
+    n = 6000
+    o = rng.uniform(-60, 60, (n, 3)).astype(np.float32); o[:, 1] = rng.uniform(0.05, 40.0, n)   # mostly outside the grid
+    tgt = rng.uniform(-9, 9, (n, 3)).astype(np.float32); tgt[:, 1] = rng.uniform(-0.5, 1.5, n)
+    d = (tgt - o).astype(np.float32)
+    d[n // 2:] = rng.normal(0, 1, (n - n // 2, 3)).astype(np.float32)  # half of them aimed anywhere, sky included
+    want = osc.trace_rays(o, d, 0.001, 100.0)
+    assert_hits_equal(fz.hit(o, d, 0.001, 100.0), want)
+    assert (want[0] != 0).sum() > n // 4
+    # a scene whose objects tie exactly: two identical marched spheres, the first of the scan order must win
+    w = api.HittableList()
+    m = api.Material.new_lambertian((0.5, 0.5, 0.5))
+    for k in range(8):
+        w += api.MarchedSphere((float(k % 4) * 3.0, 1.0, float(k // 4) * 3.0), 1.0, m)
+        w += api.MarchedSphere((float(k % 4) * 3.0, 1.0, float(k // 4) * 3.0), 1.0, m)
+    fz2 = w.freeze(flags=freeze_flags)
+    osc2 = oracle_scene_from(O, fz2)
+    o3 = rng.uniform(-30, 30, (2000, 3)).astype(np.float32); o3[:, 1] = rng.uniform(3, 30, 2000)
+    t3 = rng.uniform(0, 9, (2000, 3)).astype(np.float32); t3[:, 1] = 1.0
+    want3 = osc2.trace_rays(o3, t3 - o3, 0.001, 100.0)
+    assert_hits_equal(fz2.hit(o3, t3 - o3, 0.001, 100.0), want3)
+    hit_ids = want3[0][want3[0] != 0]
+    assert hit_ids.size > 500 and ((hit_ids & np.uint64(0xFFFFFFFF)) % np.uint64(2) == 1).all()  # index+1 odd = the first of each pair
