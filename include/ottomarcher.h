@@ -244,6 +244,10 @@ OM_API om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out,
 #define OM_FREEZE_STATIC_PADDING (1u << 2)
 /* no distance BVH over the marched objects (min_j |sdf_j| by the full scan outside the candidate grid) */
 #define OM_FREEZE_NO_MARCHED_BVH (1u << 3)
+/* build the BVH over the traced primitives on the current CUDA device (Morton order + Karras' parallel
+ * hierarchy) instead of the host's binned-SAH builder: a 10^6-sphere freeze drops from seconds to tens of
+ * milliseconds, the tree traverses somewhat slower.  Needs a device (OM_ERR_NO_DEVICE / OM_ERR_CUDA).     */
+#define OM_FREEZE_GPU_BVH (1u << 4)
 OM_API om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags);
 /* statistics of the frozen scene: [0] bvh nodes, [1] bvh depth, [2] primitives in the BVH,
  * [3] primitives kept in the always-test list, [4] bytes of the device scene image,

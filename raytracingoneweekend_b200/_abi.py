@@ -27,6 +27,7 @@ RENDER_BRUTE_FORCE = 1 << 2
 RENDER_WAVEFRONT = 1 << 3
 RENDER_PERSISTENT = 1 << 6
 FREEZE_NO_ALWAYS_LIST, FREEZE_RAY_PADDING, FREEZE_STATIC_PADDING, FREEZE_NO_MARCHED_BVH = 1, 2, 4, 8
+FREEZE_GPU_BVH = 16
 RENDER_NO_SMEM_SCENE = 1 << 4
 RENDER_COUNTERS = 1 << 5
 

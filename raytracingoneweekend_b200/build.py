@@ -21,6 +21,7 @@ SOURCES = [  # (file, extra flags)
     ("om_kernels_fast.cu", []),
     ("om_kernels_exact.cu", ["-fmad=false"]),
     ("om_api.cu", ["-fmad=false"]),
+    ("om_lbvh.cu", []),
     ("om_host.cpp", []),
     ("om_scene.cpp", []),
     ("om_bvh.cpp", []),

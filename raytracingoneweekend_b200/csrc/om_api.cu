@@ -189,7 +189,9 @@ om_status om_scene_generate(om_scene* s, uint32_t kind, uint64_t seed, uint64_t 
 om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags) {
     if (!s) return fail(OM_ERR_INVALID, "om_scene_freeze: NULL scene");
     s->release_device();
-    oms::freeze(s->lists, cam, flags, s->fz);
+    s->frozen = false;
+    const std::string err = oms::freeze(s->lists, cam, flags, s->fz);
+    if (!err.empty()) return fail(om_device_count() > 0 ? OM_ERR_CUDA : OM_ERR_NO_DEVICE, "om_scene_freeze: %s", err.c_str());
     s->frozen = true;
     return OM_OK;
 }

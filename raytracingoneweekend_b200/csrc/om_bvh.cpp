@@ -3,12 +3,15 @@
 #include <math.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <limits>
 
 namespace omb {
 namespace {
 
 constexpr int kBins = 16;
+constexpr uint32_t kBalanceDepth = 34;
 const float kInf = std::numeric_limits<float>::infinity();
 
 struct Box {
@@ -32,7 +35,7 @@ struct Item {
 struct Builder {
     const std::vector<uint32_t>& refs;
     const std::vector<Aabb>& boxes;
-    std::vector<Item> items;
+    std::vector<Item>& items;  // shared; a builder only touches its own range
     std::vector<Node>& nodes;
     uint32_t max_depth = 0;
 
@@ -101,7 +104,17 @@ struct Builder {
     int32_t build_range(size_t b, size_t e, uint32_t depth) {
         max_depth = std::max(max_depth, depth);
         if (e - b == 1) return ~int32_t(refs[items[b].prim]);
-        const size_t mid = split(b, e);
+        // SAH can peel one object per level off a badly spread set; the traversal stacks hold 64 entries, so below
+        // kBalanceDepth the ranges are halved instead (at most 28 more levels for any count a ref can index)
+        size_t mid;
+        if (depth >= kBalanceDepth) {
+            Box cb;
+            for (size_t i = b; i < e; i++) cb.grow_pt(items[i].c);
+            int ax = 0;
+            for (int a = 1; a < 3; a++) if (cb.hi[a] - cb.lo[a] > cb.hi[ax] - cb.lo[ax]) ax = a;
+            mid = b + (e - b) / 2;
+            std::nth_element(items.begin() + b, items.begin() + mid, items.begin() + e, [ax](const Item& x, const Item& y) { return x.c[ax] < y.c[ax]; });
+        } else mid = split(b, e);
         const int32_t me = int32_t(nodes.size());
         nodes.push_back(Node());
         const Box lb = bounds(b, mid), rb = bounds(mid, e);
@@ -116,17 +129,60 @@ struct Builder {
 
 }  // namespace
 
+// Large inputs: the top of the tree is split on the calling thread down to ranges of a few thousand objects, the
+// subtrees under it are built by a pool of threads into their own arrays (disjoint item ranges), then appended with
+// their indices shifted.  Same splits as the serial build, so the same tree (node order aside).
+namespace {
+struct Sub {
+    size_t b, e;
+    uint32_t depth;
+    std::vector<Node> nodes;
+    int32_t root = 0;
+    uint32_t max_depth = 0;
+};
+struct TopBuilder {
+    Builder& bld;
+    std::vector<Sub>& subs;
+    std::vector<int32_t> ltask, rtask;  // per top node: index of the Sub that hangs under the left / right child, or -1
+    size_t grain;
+    int32_t go(size_t b, size_t e, uint32_t depth, int32_t* task_out) {
+        *task_out = -1;
+        if (e - b == 1) return ~int32_t(bld.refs[bld.items[b].prim]);
+        if (e - b <= grain || depth >= 12) {
+            Sub s; s.b = b; s.e = e; s.depth = depth;
+            subs.push_back(std::move(s));
+            *task_out = int32_t(subs.size() - 1);
+            return 0;
+        }
+        const size_t mid = bld.split(b, e);
+        const int32_t me = int32_t(bld.nodes.size());
+        bld.nodes.push_back(Node());
+        ltask.push_back(-1); rtask.push_back(-1);
+        const Box lb = bld.bounds(b, mid), rb = bld.bounds(mid, e);
+        int32_t lt, rt;
+        const int32_t l = go(b, mid, depth + 1, &lt);
+        const int32_t r = go(mid, e, depth + 1, &rt);
+        Node& n = bld.nodes[size_t(me)];
+        for (int a = 0; a < 3; a++) { n.lmin[a] = lb.lo[a]; n.lmax[a] = lb.hi[a]; n.rmin[a] = rb.lo[a]; n.rmax[a] = rb.hi[a]; }
+        n.left = l; n.right = r; n.pad0 = n.pad1 = 0;
+        ltask[size_t(me)] = lt; rtask[size_t(me)] = rt;
+        bld.max_depth = std::max(bld.max_depth, depth);
+        return me;
+    }
+};
+}  // namespace
+
 void build(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, BuildResult& out) {
     out.nodes.clear();
     out.depth = 0;
     const size_t n = refs.size();
     if (n == 0) return;
     out.nodes.reserve(n);
-    Builder bld{refs, boxes, {}, out.nodes};
-    bld.items.resize(n);
+    std::vector<Item> items(n);
+    Builder bld{refs, boxes, items, out.nodes};
     for (size_t i = 0; i < n; i++) {
-        bld.items[i].prim = uint32_t(i);
-        for (int a = 0; a < 3; a++) bld.items[i].c[a] = 0.5f * (boxes[i].lo[a] + boxes[i].hi[a]);
+        items[i].prim = uint32_t(i);
+        for (int a = 0; a < 3; a++) items[i].c[a] = 0.5f * (boxes[i].lo[a] + boxes[i].hi[a]);
     }
     if (n == 1) {  // a root with one real child and one empty child
         Node root;
@@ -136,8 +192,54 @@ void build(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, Bu
         out.depth = 1;
         return;
     }
-    bld.build_range(0, n, 1);
-    out.depth = bld.max_depth;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    if (n < 65536 || hw < 2) {
+        bld.build_range(0, n, 1);
+        out.depth = bld.max_depth;
+        return;
+    }
+    std::vector<Sub> subs;
+    TopBuilder top{bld, subs, {}, {}, std::max<size_t>(4096, n / (8 * size_t(hw)))};
+    int32_t root_task;
+    top.go(0, n, 1, &root_task);  // (n >= 65536 > grain: the root is a top node)
+    std::atomic<size_t> next{0};
+    auto worker = [&]() {
+        for (;;) {
+            const size_t k = next.fetch_add(1);
+            if (k >= subs.size()) return;
+            Sub& s = subs[k];
+            s.nodes.reserve(s.e - s.b);
+            Builder sb{refs, boxes, items, s.nodes};
+            s.root = sb.build_range(s.b, s.e, s.depth);
+            s.max_depth = sb.max_depth;
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < std::min<unsigned>(hw, 32u); t++) pool.emplace_back(worker);
+    worker();
+    for (auto& t : pool) t.join();
+    // append the subtrees; their inner-node indices move by the offset, leaves (negative) stay
+    const size_t n_top = out.nodes.size();
+    std::vector<int32_t> offset(subs.size());
+    size_t at = n_top;
+    for (size_t k = 0; k < subs.size(); k++) { offset[k] = int32_t(at); at += subs[k].nodes.size(); }
+    out.nodes.resize(at);
+    uint32_t depth = bld.max_depth;
+    for (size_t k = 0; k < subs.size(); k++) {
+        Node* dst = out.nodes.data() + offset[k];
+        for (size_t i = 0; i < subs[k].nodes.size(); i++) {
+            Node nd = subs[k].nodes[i];
+            if (nd.left >= 0) nd.left += offset[k];
+            if (nd.right >= 0) nd.right += offset[k];
+            dst[i] = nd;
+        }
+        depth = std::max(depth, subs[k].max_depth);
+    }
+    for (size_t i = 0; i < n_top; i++) {
+        if (top.ltask[i] >= 0) { const Sub& s = subs[size_t(top.ltask[i])]; out.nodes[i].left = s.root >= 0 ? s.root + offset[size_t(top.ltask[i])] : s.root; }
+        if (top.rtask[i] >= 0) { const Sub& s = subs[size_t(top.rtask[i])]; out.nodes[i].right = s.root >= 0 ? s.root + offset[size_t(top.rtask[i])] : s.root; }
+    }
+    out.depth = depth;
 }
 
 }  // namespace omb

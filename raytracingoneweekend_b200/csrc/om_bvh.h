@@ -33,4 +33,9 @@ struct BuildResult {
 // refs[i] / boxes[i] describe primitive i.  Binned SAH, one primitive per leaf.
 void build(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, BuildResult& out);
 
+// The same tree shape contract built on the current CUDA device (om_lbvh.cu): Morton order + Karras' hierarchy.
+// false = not built, `err` says why (a CUDA error, fewer than 2 primitives, a non-finite box, or a tree deeper
+// than max_depth, which the traversal stacks could not hold).
+bool build_gpu(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, BuildResult& out, uint32_t max_depth, char* err, size_t errlen);
+
 }  // namespace omb

@@ -3,7 +3,11 @@
 #include <math.h>
 #include <string.h>
 
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <algorithm>
+#include <chrono>
 #include <limits>
 
 #include "om_bvh.h"
@@ -333,12 +337,21 @@ void build_marched_bvh(const omh::SceneLists& L, omd::SceneHeader& h, Packer& co
 }
 }  // namespace
 
-void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, FrozenScene& out) {
+std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, FrozenScene& out) {
     using namespace omd;
     SceneHeader& h = out.hdr;
     memset(&h, 0, sizeof h);
     out.hot.clear();
     out.cold.clear();
+    // OM_FREEZE_TIMING=1 (development): seconds spent per phase, to stderr
+    const bool timing = getenv("OM_FREEZE_TIMING") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[om freeze] %-22s %.3f s\n", what, std::chrono::duration<double>(now - t_prev).count());
+        t_prev = now;
+    };
     h.n[PT_SPHERE] = uint32_t(L.spheres.size());   h.n[PT_CUBE] = uint32_t(L.cubes.size());
     h.n[PT_TRI] = uint32_t(L.triangles.size());    h.n[PT_PLANE] = uint32_t(L.infinite_planes.size());
     h.n[PT_PARA] = uint32_t(L.parallelograms.size());
@@ -395,6 +408,8 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
     if (dyn) reach = 0.0;
     std::vector<uint32_t> refs;
     std::vector<Aabb> boxes;
+    refs.reserve(L.spheres.size() + L.cubes.size() + L.triangles.size() + L.parallelograms.size());
+    boxes.reserve(refs.capacity());
     for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i], reach)); }
     for (size_t i = 0; i < L.cubes.size(); i++) { refs.push_back(make_ref(PT_CUBE, uint32_t(i))); boxes.push_back(cube_box(L.cubes[i], reach)); }
     for (size_t i = 0; i < L.triangles.size(); i++) { refs.push_back(make_ref(PT_TRI, uint32_t(i))); boxes.push_back(bary_box(L.triangles[i], false, reach)); }
@@ -417,14 +432,24 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
         refs.swap(r2); boxes.swap(b2);
     }
     std::sort(large.begin(), large.end());
+    lap("boxes + always list");
     omb::BuildResult bvh;
-    omb::build(refs, boxes, bvh);
+    bool built = false;
+    if ((flags & 16u) && refs.size() >= 2) {
+        char why[256] = "";
+        built = omb::build_gpu(refs, boxes, bvh, 60, why, sizeof why);
+        // a tree too deep for the traversal stacks or a non-finite box falls to the host builder; a CUDA failure is an error
+        if (!built && strstr(why, ": ")) return std::string(why);
+    }
+    if (!built) omb::build(refs, boxes, bvh);
     h.n_nodes = uint32_t(bvh.nodes.size());
     h.n_large = uint32_t(large.size());
     h.n_bvh_prims = uint32_t(refs.size());
     h.bvh_depth = bvh.depth;
 
+    lap(built ? "bvh (device)" : "bvh (host)");
     // ---- hot image ----------------------------------------------------------------------------
+    out.hot.reserve(16 * bvh.nodes.size() + 12 * (L.spheres.size() + L.cubes.size()) + 16 * (L.triangles.size() + L.parallelograms.size()) + 4096);
     Packer hot(out.hot);
     h.off_nodes = hot.units();
     for (const omb::Node& nd : bvh.nodes) {
@@ -510,6 +535,7 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
     h.hot_units = hot.units();
 
     // ---- cold image ---------------------------------------------------------------------------
+    out.cold.reserve(12 * (L.spheres.size() + L.cubes.size()) + 8 * out.n_total + 4096);
     Packer cold(out.cold);
     h.off_sph_l2w = cold.units();
     for (const om_sphere& s : L.spheres) cold.rows3(s.m_local_to_world);
@@ -524,12 +550,15 @@ void freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flags, Froz
     };
     mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
     mats(PT_PARA, L.parallelograms); mats(PT_MSPHERE, L.marched_spheres); mats(PT_MBOX, L.marched_boxes); mats(PT_MTORUS, L.marched_tori);
+    lap("pack hot + cold images");
     build_marched_grid(L, h, cold);
     if (!(flags & 8u)) build_marched_bvh(L, h, cold);
     if (cold.units() == 0) cold.f4(0, 0, 0, 0);
     if (hot.units() == 0) hot.f4(0, 0, 0, 0);
     h.hot_units = hot.units();
     h.cold_units = cold.units();
+    lap("marched structures");
+    return std::string();
 }
 
 }  // namespace oms

@@ -429,3 +429,51 @@ def test_marched_distance_bvh_hit_bit_exact(api, A, O, freeze_flags):
     assert_hits_equal(fz2.hit(o3, t3 - o3, 0.001, 100.0), want3)
     hit_ids = want3[0][want3[0] != 0]
     assert hit_ids.size > 500 and ((hit_ids & np.uint64(0xFFFFFFFF)) % np.uint64(2) == 1).all()  # index+1 odd = the first of each pair
+
+
+def test_gpu_bvh_build_same_results(api, A, O, rtiow):
+    """OM_FREEZE_GPU_BVH: Morton/Karras tree built on the device instead of the host's binned SAH; the tree only culls,
+    so hits and images must not change by a bit."""
+    fz = api.FrozenHittableList.generate("many_spheres", 5, 20000, flags=A.FREEZE_GPU_BVH)
+    st = fz.stats()
+    assert st["bvh_nodes"] == st["bvh_prims"] - 1 and 10 < st["bvh_depth"] <= 60
+    osc = oracle_scene_from(O, fz)
+    rng = np.random.default_rng(4)
+    o = np.tile(np.array([60, 12, 14], np.float32), (4000, 1))
+    tgt = rng.uniform(-40, 40, (4000, 3)).astype(np.float32); tgt[:, 1] = rng.uniform(0, 4, 4000)
+    assert_hits_equal(fz.hit(o, tgt - o, 0.001, 1000.0, flags=0), osc.trace_rays(o, tgt - o, 0.001, 1000.0))
+    # every primitive type, and both pipelines, on the RTIOW scene
+    g = api.FrozenHittableList.generate("random_scene", 1, flags=A.FREEZE_GPU_BVH)
+    cam = cam_rtiow(api)
+    want = None
+    for scene in (rtiow[0], g):
+        for flags in (A.RENDER_PERSISTENT, A.RENDER_WAVEFRONT):
+            r = api.Renderer(scene, cam, api.render_params(240, 160, 8, seed=21, flags=flags))
+            r.launch(0); px = r.read_pixels(); r.close()
+            if want is None:
+                want = px
+            else:
+                assert_pixels_equal(px, want)
+    # duplicate centres (equal Morton keys are told apart by position)
+    w = api.HittableList()
+    m = api.Material.new_lambertian((0.5, 0.5, 0.5))
+    for k in range(40):
+        w += api.Sphere.new_with_radius((float(k % 5), 0.0, -3.0), 0.3 + 0.01 * (k // 5), m)
+    d1, d0 = w.freeze(flags=A.FREEZE_GPU_BVH), w.freeze()
+    o2, dd2 = rays_at_scene(3000, 8)
+    o2[:] = (2.0, 0.5, 4.0)
+    assert_hits_equal(d1.hit(o2, dd2), d0.hit(o2, dd2))
+
+
+@pytest.mark.parametrize("freeze_flags", [0, 16])  # host build (threaded above 65536 objects) / device build
+def test_large_bvh_equals_linear_scan(api, A, freeze_flags):
+    fz = api.FrozenHittableList.generate("many_spheres", 7, 100000, flags=freeze_flags)
+    st = fz.stats()
+    assert st["bvh_nodes"] == st["bvh_prims"] - 1 and st["bvh_depth"] <= 60
+    rng = np.random.default_rng(14)
+    n = 3000
+    o = rng.uniform(-90, 90, (n, 3)).astype(np.float32); o[:, 1] = rng.uniform(0.2, 12.0, n)
+    tgt = rng.uniform(-90, 90, (n, 3)).astype(np.float32); tgt[:, 1] = rng.uniform(0, 4, n)
+    got = fz.hit(o, tgt - o, 0.001, 100.0)
+    assert_hits_equal(got, fz.hit(o, tgt - o, 0.001, 100.0, flags=A.RENDER_BRUTE_FORCE))
+    assert (got[0] != 0).sum() > n // 5

@@ -149,3 +149,22 @@ def test_product_does_not_use_the_oracle():
         src = open(f, errors="replace").read()
         for pat in banned:
             assert not re.search(pat, src, re.M), (f, pat)
+
+
+def test_gpu_bvh_build_fails_loudly_without_a_device(api, A):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present")
+    with pytest.raises(Exception) as e:
+        api.FrozenHittableList.generate("many_spheres", 5, 100, flags=A.FREEZE_GPU_BVH)
+    assert "GPU BVH build" in str(e.value)
+
+
+def test_host_bvh_depth_stays_below_the_traversal_stack(api, A):
+    """Exponentially spread spheres make SAH peel one object per level; the builder has to switch to halving."""
+    w = api.HittableList()
+    m = api.Material.new_lambertian((0.5, 0.5, 0.5))
+    for k in range(-100, 101):
+        w += api.Sphere.new_with_radius((2.0 ** k, 0.0, 0.0), 0.1 * 2.0 ** k, m)
+    st = w.freeze(flags=A.FREEZE_NO_ALWAYS_LIST).stats()
+    assert st["bvh_prims"] == 201 and st["bvh_depth"] <= 62
