@@ -312,6 +312,20 @@ OM_API om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_
  * colour (utils.rs:12-17).                                                                   */
 OM_API om_status om_render_export_accum(om_render* r, float* dev_acc, uint64_t* dev_bloom);
 OM_API om_status om_render_import_accum(om_render* r, const float* dev_acc, const uint64_t* dev_bloom);
+/* Adaptive sampling across GPUs (render_thread.rs:68-102,194-200 at multi-GPU scale): pixels retire at
+ * different times, so the live ones are re-dealt between passes.  Every handle is created over the WHOLE
+ * frame (no static partition); before each pass the caller gives all of them the same chunk -> owner
+ * table (one byte per OM_CHUNK_PIXELS pixels) and its own id, a pass then renders the live pixels of
+ * the chunks it owns; afterwards om_render_export_state(only_owned = 1) writes 8 words per pixel
+ * {sum.rgb, n, avg_depth, bad_avgs, bloom lo, hi} bit for bit with zeros for other owners' pixels, an
+ * integer SUM over the ranks (NCCL all-reduce) reassembles the frame, om_render_import_state loads it
+ * into every handle, and om_render_live_per_chunk says how many pixels of each chunk still want samples
+ * (the input of the next deal).  Results are those of one handle rendering alone, bit for bit.
+ * owners == NULL returns the handle to the static rule of om_render_params.                          */
+OM_API om_status om_render_set_chunk_owners(om_render* r, const uint8_t* owners, size_t n_chunks, uint32_t my_id);
+OM_API om_status om_render_export_state(om_render* r, uint32_t* dev_state, uint32_t only_owned);
+OM_API om_status om_render_import_state(om_render* r, const uint32_t* dev_state);
+OM_API om_status om_render_live_per_chunk(om_render* r, uint32_t* host_counts, size_t n_chunks);
 /* dst[i] |= src[k][i] for k < nsrc: the bitwise-OR NCCL does not have. Device pointers.       */
 OM_API om_status om_bloom_or(uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc, size_t n,
                              int32_t device);

@@ -55,6 +55,10 @@ PROTOTYPES = {
     "om_render_export_accum": ("st", [vp, vp, vp]),
     "om_render_import_accum": ("st", [vp, vp, vp]),
     "om_bloom_or": ("st", [vp, vp, sz, sz, i32]),
+    "om_render_set_chunk_owners": ("st", [vp, vp, sz, u32]),
+    "om_render_export_state": ("st", [vp, vp, u32]),
+    "om_render_import_state": ("st", [vp, vp]),
+    "om_render_live_per_chunk": ("st", [vp, vp, sz]),
     "om_trace_rays": ("st", [vp, vp, vp, sz, f32, f32, u32, i32, vp, vp, vp, vp]),
     "om_camera_new": (None, [P(A.Camera), F3, F3, F3, f32, f32, f32, f32]),
     "om_material_lambertian": (None, [P(A.Material), F3]),

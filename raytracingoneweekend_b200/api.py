@@ -346,6 +346,30 @@ class Renderer:
     def import_accum(self, dev_acc_ptr, dev_bloom_ptr):
         _lib.call("om_render_import_accum", self.h, dev_acc_ptr, dev_bloom_ptr)
 
+    # ---- adaptive sampling across GPUs (dist.AdaptiveScheduler) ----
+    @property
+    def n_chunks(self):
+        return (self.npx + A.CHUNK_PIXELS - 1) // A.CHUNK_PIXELS
+
+    def set_chunk_owners(self, owners, my_id):
+        """owners: uint8 array, one entry per 2730-pixel chunk (None: back to the static partition)."""
+        if owners is None:
+            _lib.call("om_render_set_chunk_owners", self.h, None, 0, 0)
+            return
+        o = np.ascontiguousarray(owners, np.uint8)
+        _lib.call("om_render_set_chunk_owners", self.h, o.ctypes.data, o.shape[0], my_id)
+
+    def export_state(self, dev_state_ptr, only_owned=True):
+        _lib.call("om_render_export_state", self.h, dev_state_ptr, 1 if only_owned else 0)
+
+    def import_state(self, dev_state_ptr):
+        _lib.call("om_render_import_state", self.h, dev_state_ptr)
+
+    def live_per_chunk(self):
+        c = np.zeros(self.n_chunks, np.uint32)
+        _lib.call("om_render_live_per_chunk", self.h, c.ctypes.data, c.shape[0])
+        return c
+
 
 def render(camera, world, max_depth, tmin, tmax, samples_per_pixel, image_width, image_height, seed=0, flags=A.RENDER_ADAPTIVE, device=-1):
     """render_thread::render (render_thread.rs:145-147) for all threads at once; returns the Vec<Pixel>

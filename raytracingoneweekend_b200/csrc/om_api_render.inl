@@ -73,12 +73,18 @@ __global__ void k_bloom_or(unsigned long long* __restrict__ dst, const unsigned 
 }
 // ThreadPixels::add_run / swap_buffers (render_thread.rs:92-101) for the whole image: the list
 // of pixels that still want samples, by warp ballot + popc and one atomic per warp.
+// Who owns pixel i: the chunk owner table when one is set (om_render_set_chunk_owners), else the interleaved-chunk rule.
+__device__ __forceinline__ bool pixel_is_mine(uint32_t i, uint32_t part_rank, uint32_t part_world, const uint8_t* __restrict__ owners, uint32_t my_id) {
+    if (owners) return owners[i / OM_CHUNK_PIXELS] == my_id;
+    return part_world <= 1u || ((i / OM_CHUNK_PIXELS) % part_world) == part_rank;
+}
 __global__ void k_compact_live(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t npx, uint32_t budget, uint32_t adaptive,
-                               uint32_t part_rank, uint32_t part_world, uint32_t* __restrict__ list, uint32_t* __restrict__ count) {
+                               uint32_t part_rank, uint32_t part_world, const uint8_t* __restrict__ owners, uint32_t my_id, uint32_t* __restrict__ list,
+                               uint32_t* __restrict__ count) {
     const uint32_t i = blockIdx.x * UT + threadIdx.x;
     bool live = false;
     if (i < npx) {
-        const bool mine = part_world <= 1u || ((i / OM_CHUNK_PIXELS) % part_world) == part_rank;
+        const bool mine = pixel_is_mine(i, part_rank, part_world, owners, my_id);
         const uint32_t n = __float_as_uint(acc[i].w);
         live = mine && n < budget && !(adaptive && aux[i].y >= 5u);
     }
@@ -88,6 +94,35 @@ __global__ void k_compact_live(const float4* __restrict__ acc, const uint4* __re
     if (lane == 0u && m) base = atomicAdd(count, (uint32_t)__popc(m));
     base = __shfl_sync(0xffffffffu, base, 0);
     if (live) list[base + __popc(m & ((1u << lane) - 1u))] = i;
+}
+// ---- multi-GPU adaptive scheduling: raw pixel state in and out, live pixels per chunk -------------------------------
+// 8 words per pixel = {sum.r, sum.g, sum.b, n, avg_depth, bad_avgs, bloom lo, bloom hi}, bit for bit; pixels of other
+// owners are written as zeros so that an integer SUM over the ranks reassembles the frame exactly.
+__global__ void k_export_state(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint4* __restrict__ out, uint32_t npx, uint32_t only_owned,
+                               uint32_t part_rank, uint32_t part_world, const uint8_t* __restrict__ owners, uint32_t my_id) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    uint4 a = make_uint4(0u, 0u, 0u, 0u), b = a;
+    if (!only_owned || pixel_is_mine(i, part_rank, part_world, owners, my_id)) {
+        const float4 f = acc[i];
+        a = make_uint4(__float_as_uint(f.x), __float_as_uint(f.y), __float_as_uint(f.z), __float_as_uint(f.w));
+        b = aux[i];
+    }
+    out[2u * i] = a; out[2u * i + 1u] = b;
+}
+__global__ void k_import_state(float4* __restrict__ acc, uint4* __restrict__ aux, const uint4* __restrict__ in, uint32_t npx) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    const uint4 a = in[2u * i];
+    acc[i] = make_float4(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z), __uint_as_float(a.w));
+    aux[i] = in[2u * i + 1u];
+}
+__global__ void k_live_per_chunk(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t npx, uint32_t budget, uint32_t adaptive,
+                                 uint32_t* __restrict__ counts) {
+    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    if (i >= npx) return;
+    const uint32_t n = __float_as_uint(acc[i].w);
+    if (n < budget && !(adaptive && aux[i].y >= 5u)) atomicAdd(&counts[i / OM_CHUNK_PIXELS], 1u);
 }
 // ---- draw_to_sdl's display modes (main.rs:361-437) and its three weighted 3x3 filters (main.rs:219-343) ----
 // reductions of MODE_SHOW_SAMPLES / MODE_SHOW_DEPTH: red[0] = max n (starts at 1), red[1] = bits of the largest finite
@@ -223,6 +258,9 @@ struct om_render {
     uint4* aux = nullptr;
     uint8_t* jitter = nullptr;
     unsigned long long* counters = nullptr;
+    uint8_t* owners = nullptr;   // chunk -> owner id table (om_render_set_chunk_owners), device
+    uint32_t owner_id = 0;
+    uint32_t* chunk_counts = nullptr;
     uint32_t* live_list = nullptr;
     uint32_t* live_count = nullptr;
     bool have_live = false;
@@ -314,7 +352,7 @@ om_status om_render_destroy(om_render* r) {
     if (r->stream) cudaStreamSynchronize(r->stream);
     for (EventPair& e : r->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (EventPair& e : r->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    cudaFree(r->acc); cudaFree(r->aux); cudaFree(r->jitter); cudaFree(r->counters); cudaFree(r->live_list); cudaFree(r->live_count); cudaFree(r->staging);
+    cudaFree(r->acc); cudaFree(r->aux); cudaFree(r->jitter); cudaFree(r->counters); cudaFree(r->live_list); cudaFree(r->live_count); cudaFree(r->owners); cudaFree(r->chunk_counts); cudaFree(r->staging);
     if (r->wf.n_slots) {
         cudaFree(r->wf.s_ray); cudaFree(r->wf.s_st); cudaFree(r->wf.s_live);
         cudaFree(r->wf.q_ray[0]); cudaFree(r->wf.q_ray[1]); cudaFree(r->wf.q_march[0]); cudaFree(r->wf.q_march[1]); cudaFree(r->wf.q_shade[0]); cudaFree(r->wf.q_shade[1]); cudaFree(r->wf.ctr);
@@ -537,7 +575,15 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     omk::RenderArgs a = make_args(r);
     a.spp_pass = spp_this_pass ? spp_this_pass : r->budget;
     const bool adaptive = (r->p.flags & OM_RENDER_ADAPTIVE) != 0;
-    if (adaptive && r->have_live) { a.live_list = r->live_list; a.live_count = r->live_count; }
+    if (r->owners) {  // scheduled ownership: the pixels to walk are decided now, from the state and the table of this moment
+        if (!r->live_list) { CU(cudaMalloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t))); CU(cudaMalloc(&r->live_count, sizeof(uint32_t))); }
+        CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
+        k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, adaptive ? 1u : 0u, 0u, 1u, r->owners, r->owner_id, r->live_list, r->live_count);
+        CU(cudaGetLastError());
+        r->kernels++;
+        r->have_live = true;
+    }
+    if ((adaptive || r->owners) && r->have_live) { a.live_list = r->live_list; a.live_count = r->live_count; }
     EventPair ev;
     if (!r->pool.empty()) { ev = r->pool.back(); r->pool.pop_back(); }
     else { CU(cudaEventCreate(&ev.a)); CU(cudaEventCreate(&ev.b)); }
@@ -555,9 +601,9 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
         r->kernels++;
     }
     r->n_uniform = n_target;
-    if (adaptive) {  // next pass walks only the pixels that still want samples
+    if (adaptive && !r->owners) {  // next pass walks only the pixels that still want samples
         CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
-        k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, r->live_list, r->live_count);
+        k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, nullptr, 0u, r->live_list, r->live_count);
         CU(cudaGetLastError());
         r->kernels++;
         r->have_live = true;
@@ -709,6 +755,53 @@ om_status om_render_import_accum(om_render* r, const float* dev_acc, const uint6
     CU(cudaSetDevice(r->dev));
     k_import_accum<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, (const float4*)dev_acc, (const unsigned long long*)dev_bloom, r->npx);
     CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+om_status om_render_set_chunk_owners(om_render* r, const uint8_t* owners, size_t n_chunks, uint32_t my_id) {
+    if (!r) return fail(OM_ERR_INVALID, "om_render_set_chunk_owners: NULL handle");
+    CU(cudaSetDevice(r->dev));
+    const size_t chunks = (size_t(r->npx) + OM_CHUNK_PIXELS - 1) / OM_CHUNK_PIXELS;
+    if (!owners) {  // back to the static rule of om_render_params
+        CU(cudaStreamSynchronize(r->stream));
+        cudaFree(r->owners); r->owners = nullptr; r->have_live = false;
+        return OM_OK;
+    }
+    if (n_chunks != chunks) return fail(OM_ERR_INVALID, "om_render_set_chunk_owners: the image has %zu chunks of %u pixels, got %zu", chunks, OM_CHUNK_PIXELS, n_chunks);
+    if (r->p.part_world > 1u || r->p.sample_base || r->p.sample_count) return fail(OM_ERR_INVALID, "om_render_set_chunk_owners: the handle must own the whole frame (no static partition)");
+    if (!r->owners) CU(cudaMalloc(&r->owners, chunks));
+    CU(cudaMemcpyAsync(r->owners, owners, chunks, cudaMemcpyHostToDevice, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    r->owner_id = my_id;
+    return OM_OK;
+}
+om_status om_render_export_state(om_render* r, uint32_t* dev_state, uint32_t only_owned) {
+    if (!r || !dev_state) return fail(OM_ERR_INVALID, "om_render_export_state: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    k_export_state<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, (uint4*)dev_state, r->npx, only_owned, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, r->owners, r->owner_id);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+om_status om_render_import_state(om_render* r, const uint32_t* dev_state) {
+    if (!r || !dev_state) return fail(OM_ERR_INVALID, "om_render_import_state: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    k_import_state<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, (const uint4*)dev_state, r->npx);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(r->stream));
+    r->have_live = false;
+    return OM_OK;
+}
+om_status om_render_live_per_chunk(om_render* r, uint32_t* host_counts, size_t n_chunks) {
+    if (!r || !host_counts) return fail(OM_ERR_INVALID, "om_render_live_per_chunk: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    const size_t chunks = (size_t(r->npx) + OM_CHUNK_PIXELS - 1) / OM_CHUNK_PIXELS;
+    if (n_chunks != chunks) return fail(OM_ERR_INVALID, "om_render_live_per_chunk: the image has %zu chunks, got %zu", chunks, n_chunks);
+    if (!r->chunk_counts) CU(cudaMalloc(&r->chunk_counts, chunks * sizeof(uint32_t)));
+    CU(cudaMemsetAsync(r->chunk_counts, 0, chunks * sizeof(uint32_t), r->stream));
+    k_live_per_chunk<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, (r->p.flags & OM_RENDER_ADAPTIVE) ? 1u : 0u, r->chunk_counts);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(host_counts, r->chunk_counts, chunks * sizeof(uint32_t), cudaMemcpyDeviceToHost, r->stream));
     CU(cudaStreamSynchronize(r->stream));
     return OM_OK;
 }

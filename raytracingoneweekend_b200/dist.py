@@ -116,3 +116,83 @@ class DistributedRenderer:
 
     def close(self):
         self.r.close()
+
+
+# ---- adaptive sampling across GPUs -------------------------------------------------------------
+def deal_chunks(live_counts, world):
+    """Chunk -> rank table for the next pass from the live pixels per chunk (identical on every rank): largest chunk
+    first onto the rank with the fewest live pixels so far (ties: lower rank), which balances the counts and scatters
+    every rank over the image like the reference's round-robin does (main.rs:172-189).  Chunks without live pixels
+    keep the round-robin owner; nobody renders them."""
+    counts = np.asarray(live_counts, dtype=np.int64)
+    owners = (np.arange(counts.shape[0]) % max(world, 1)).astype(np.uint8)
+    load = np.zeros(max(world, 1), np.int64)
+    for c in np.argsort(-counts, kind="stable"):
+        if counts[c] == 0:
+            break
+        k = int(np.argmin(load))
+        owners[c] = k
+        load[k] += counts[c]
+    return owners, load
+
+
+class AdaptiveScheduler:
+    """The reference's adaptive render (a pixel retires once its 8-bit colour stood still for five samples,
+    render_thread.rs:31-38,194-200) spread over `world` GPUs with the live pixels re-dealt between passes.
+
+    Every rank holds the whole frame.  Per pass: the same chunk->rank table on every rank, `pass_spp` samples for the live
+    pixels of the chunks a rank owns, then the raw 32-byte pixel states are combined by an integer SUM all-reduce (every
+    pixel has exactly one owner, the others contribute zeros, so the sum is the owner's bits) and loaded into every handle.
+    The image is bit-identical to a single-GPU adaptive render; rank 0 can read it after any pass (`on_pass`)."""
+
+    def __init__(self, frozen, cam, width, height, spp, rank, world, pass_spp=8, device=None, rebalance=False, **kw):
+        import torch
+        from . import api
+
+        self.torch = torch
+        self.rank, self.world, self.pass_spp, self.rebalance, self.spp = rank, world, max(1, pass_spp), rebalance, spp
+        self.device = torch.cuda.current_device() if device is None else device
+        flags = kw.pop("flags", 0) | A.RENDER_ADAPTIVE
+        self.r = api.Renderer(frozen, cam, api.render_params(width, height, spp, flags=flags, device=self.device, **kw))
+        self.state = torch.empty((width * height, 8), dtype=torch.int32, device=torch.device("cuda", self.device))
+        self.owners = (np.arange(self.r.n_chunks) % max(world, 1)).astype(np.uint8)
+        self.credited = 0
+        self.history = []  # per pass: (live pixels before the pass, live pixels per rank)
+
+    def _all_reduce(self, t):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+
+    def run(self, on_pass=None):
+        torch = self.torch
+        total = self.r.npx * self.spp
+        live = self.r.live_per_chunk()
+        done_spp, seen = 0, 0
+        while done_spp < self.spp and int(live.sum()) > 0:
+            if self.rebalance:
+                self.owners, load = deal_chunks(live, self.world)
+            else:
+                load = np.array([int(live[self.owners == k].sum()) for k in range(self.world)])
+            self.history.append((int(live.sum()), load.tolist()))
+            self.r.set_chunk_owners(self.owners, self.rank)
+            self.r.launch(self.pass_spp)
+            self.r.export_state(self.state.data_ptr(), only_owned=True)
+            self._all_reduce(self.state)
+            if self.world > 1:
+                torch.cuda.synchronize(self.device)
+            self.r.import_state(self.state.data_ptr())
+            mine = self.r.samples_done()
+            delta = torch.tensor([mine - seen], dtype=torch.int64, device=self.state.device)
+            seen = mine
+            self._all_reduce(delta)
+            self.credited += int(delta.item())  # the AtomicU64 of main.rs:148, summed over the ranks
+            done_spp += self.pass_spp
+            live = self.r.live_per_chunk()
+            if on_pass is not None:
+                on_pass(self)
+        assert self.credited <= total
+        return self.credited
+
+    def close(self):
+        self.r.close()

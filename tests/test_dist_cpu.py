@@ -90,3 +90,57 @@ def test_partition_helpers():
     assert acc[0, 4] == 0 and np.isinf(acc[1, 4]) and acc[2, 4] == 4.0 and bloom.dtype == np.int64
     acc2, bloom2 = D.merge_accum([acc, acc], [bloom, bloom])
     assert (acc2[:, 3] == [0, 2, 4, 6]).all() and (bloom2 == bloom).all()
+
+
+# ---- adaptive scheduling across ranks (dist.AdaptiveScheduler): the host logic and the exact merge -------------------
+def test_deal_chunks_balances_and_is_deterministic():
+    from raytracingoneweekend_b200 import dist as D
+    rng = np.random.default_rng(3)
+    live = rng.integers(0, 2731, 760).astype(np.uint32)
+    live[rng.random(760) < 0.6] = 0  # most chunks already retired
+    for world in (1, 2, 3, 8):
+        owners, load = D.deal_chunks(live, world)
+        owners2, _ = D.deal_chunks(live.copy(), world)
+        assert (owners == owners2).all() and owners.dtype == np.uint8 and owners.max() < world
+        assert load.sum() == live.sum() and load.max() - load.min() <= 2730
+        dead = live == 0
+        assert (owners[dead] == (np.arange(760) % world)[dead]).all()  # retired chunks keep the round-robin owner
+        assert [int(live[owners == k].sum()) for k in range(world)] == load.tolist()
+
+
+def _state_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    from raytracingoneweekend_b200 import dist as D
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(11)  # the same "true" frame on both ranks
+    npx = 3 * 2730 + 17
+    full = rng.integers(-2**31, 2**31 - 1, (npx, 8), dtype=np.int64).astype(np.int32)
+    full[5, 0] = np.array([0x80000000], np.uint32).view(np.int32)[0]  # -0.0
+    full[6, 1] = np.array([0x7FC00001], np.uint32).view(np.int32)[0]  # a NaN payload
+    live = np.array([100, 0, 2730, 17], np.uint32)
+    owners, _ = D.deal_chunks(live, world)
+    mine = owners[np.arange(npx) // 2730] == rank
+    state = torch.from_numpy(np.where(mine[:, None], full, 0).astype(np.int32))
+    dist.all_reduce(state, op=dist.ReduceOp.SUM)  # what AdaptiveScheduler does with the exported states
+    if rank == 0:
+        q.put((state.numpy().copy(), full))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_state_merge_by_integer_sum_is_bit_exact(built):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_state_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    merged, full = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+    assert (merged == full).all()

@@ -477,3 +477,75 @@ def test_large_bvh_equals_linear_scan(api, A, freeze_flags):
     got = fz.hit(o, tgt - o, 0.001, 100.0)
     assert_hits_equal(got, fz.hit(o, tgt - o, 0.001, 100.0, flags=A.RENDER_BRUTE_FORCE))
     assert (got[0] != 0).sum() > n // 5
+
+
+@pytest.mark.parametrize("world,rebalance", [(2, True), (3, True), (2, False)])
+def test_adaptive_pixels_redealt_between_handles_bit_exact(api, A, rtiow, world, rebalance):
+    """dist.AdaptiveScheduler's protocol with the ranks emulated by `world` handles on one GPU: chunk owner table ->
+    pass -> export owned states -> integer sum -> import everywhere -> live pixels per chunk -> next deal.  The frame and
+    the credited total must be those of one handle rendering alone."""
+    import torch
+    from raytracingoneweekend_b200 import dist as D
+    fz, _ = rtiow
+    W, H, spp, pass_spp = 200, 130, 40, 8
+    cam = cam_rtiow(api, W / H)
+    p = api.render_params(W, H, spp, seed=31, flags=A.RENDER_ADAPTIVE)
+    ref = api.Renderer(fz, cam, p)
+    for _ in range(spp // pass_spp):
+        ref.launch(pass_spp)
+    want, want_credited = ref.read_pixels(), ref.samples_done()
+    ref.close()
+    assert (want["n"] < spp).any() and (want["n"] == spp).any()  # some pixels retired early, some did not
+    rs = [api.Renderer(fz, cam, p) for _ in range(world)]
+    states = [torch.empty((W * H, 8), dtype=torch.int32, device="cuda") for _ in range(world)]
+    owners = (np.arange(rs[0].n_chunks) % world).astype(np.uint8)
+    live = rs[0].live_per_chunk()
+    assert live.sum() == W * H
+    passes = 0
+    while passes * pass_spp < spp and live.sum() > 0:
+        if rebalance:
+            owners, load = D.deal_chunks(live, world)
+            assert load.max() - load.min() <= A.CHUNK_PIXELS
+        for k, r in enumerate(rs):
+            r.set_chunk_owners(owners, k)
+            r.launch(pass_spp)
+            r.export_state(states[k].data_ptr(), only_owned=True)
+        merged = states[0].clone()
+        for k in range(1, world):
+            merged += states[k]
+        torch.cuda.synchronize()
+        for r in rs:
+            r.import_state(merged.data_ptr())
+        live = rs[0].live_per_chunk()
+        assert all((r.live_per_chunk() == live).all() for r in rs[1:])
+        passes += 1
+    credited = sum(r.samples_done() for r in rs)
+    for r in rs:
+        assert_pixels_equal(r.read_pixels(), want)
+    assert credited == want_credited == W * H * spp
+    # leaving scheduled mode: the static rule is back and more passes change nothing on a finished frame
+    rs[0].set_chunk_owners(None, 0)
+    rs[0].launch(pass_spp)
+    assert_pixels_equal(rs[0].read_pixels(), want)
+    with pytest.raises(Exception):
+        rs[1].set_chunk_owners(np.zeros(3, np.uint8), 0)  # wrong table length
+    for r in rs:
+        r.close()
+
+
+def test_adaptive_scheduler_single_rank_equals_plain_render(api, A, rtiow):
+    from raytracingoneweekend_b200 import dist as D
+    fz, _ = rtiow
+    W, H, spp = 160, 100, 24
+    cam = cam_rtiow(api, W / H)
+    s = D.AdaptiveScheduler(fz, cam, W, H, spp, 0, 1, pass_spp=8, seed=77)
+    seen = []
+    credited = s.run(on_pass=lambda sch: seen.append(int(sch.r.read_pixels()["n"].sum())))
+    got = s.r.read_pixels()
+    s.close()
+    r = api.Renderer(fz, cam, api.render_params(W, H, spp, seed=77, flags=A.RENDER_ADAPTIVE))
+    r.launch(0)
+    want = r.read_pixels()
+    r.close()
+    assert_pixels_equal(got, want)
+    assert credited == W * H * spp and len(seen) == 3 and seen == sorted(seen)
