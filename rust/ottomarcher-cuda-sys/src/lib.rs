@@ -19,6 +19,11 @@ pub const OM_RENDER_NO_SMEM_SCENE: u32 = 1 << 4;
 pub const OM_RENDER_COUNTERS: u32 = 1 << 5;
 pub const OM_RENDER_WAVEFRONT: u32 = 1 << 3;
 pub const OM_RENDER_PERSISTENT: u32 = 1 << 6;
+pub const OM_FREEZE_NO_ALWAYS_LIST: u32 = 1 << 0;
+pub const OM_FREEZE_RAY_PADDING: u32 = 1 << 1;
+pub const OM_FREEZE_STATIC_PADDING: u32 = 1 << 2;
+pub const OM_FREEZE_NO_MARCHED_BVH: u32 = 1 << 3;
+pub const OM_FREEZE_GPU_BVH: u32 = 1 << 4;
 
 /// materials.rs:11-23
 #[repr(C)] #[derive(Clone, Copy, Default)]
@@ -91,6 +96,10 @@ extern "C" {
     pub fn om_write_bmp(path: *const c_char, rgb: *const u8, width: u32, height: u32) -> om_status;
     pub fn om_render_reset(r: *mut om_render) -> om_status;
     pub fn om_render_primary(r: *mut om_render, mode: u32, sample_index: u32, ids: *mut u64, t: *mut f32, n: usize) -> om_status;
+    pub fn om_render_set_chunk_owners(r: *mut om_render, owners: *const u8, n_chunks: usize, my_id: u32) -> om_status;
+    pub fn om_render_export_state(r: *mut om_render, dev_state: *mut u32, only_owned: u32) -> om_status;
+    pub fn om_render_import_state(r: *mut om_render, dev_state: *const u32) -> om_status;
+    pub fn om_render_live_per_chunk(r: *mut om_render, host_counts: *mut u32, n_chunks: usize) -> om_status;
     pub fn om_last_error() -> *const c_char;
 }
 
