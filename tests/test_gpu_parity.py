@@ -210,6 +210,16 @@ def test_render_bit_exact_fixed_spp(api, A, rtiow, W, H, spp, depth):
     r.close()
 
 
+@pytest.mark.parametrize("W,H", [(1, 1), (1, 6), (7, 1), (0, 4)])
+def test_render_rejects_one_pixel_wide_images(api, A, rtiow, W, H):
+    """u = (col + jitter) / (image_width - 1) (render_thread.rs:183-186) divides by zero on a 1-pixel-wide image: the
+    reference renders NaN rays there; the library refuses the size instead of reproducing NaN payloads."""
+    fz, _ = rtiow
+    with pytest.raises(Exception) as e:
+        api.Renderer(fz, cam_rtiow(api, 1.5), api.render_params(W, H, 4, seed=8))
+    assert "at least 2x2" in str(e.value)
+
+
 def test_render_bit_exact_adaptive_multipass(api, A, rtiow):
     """The reference's only mode: retire a pixel after 5 unchanged 8-bit colours; sample-major passes."""
     fz, osc = rtiow
