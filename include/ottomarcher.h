@@ -179,7 +179,15 @@ enum {
      * walked through L2, which wants many more rays in flight) or when it has more than 8 marched
      * objects and no distance BVH over them (OM_FREEZE_NO_MARCHED_BVH; full-scan SDF marches stall
      * the persistent kernel's warps); persistent kernel otherwise.                                */
-    OM_RENDER_PERSISTENT = 1u << 6
+    OM_RENDER_PERSISTENT = 1u << 6,
+    /* persistent kernel only: the 8 warps of each SM sub-partition meet at a named barrier at the top of
+     * the path loop and between the closest-hit query and shading, so that the warps sharing an
+     * instruction cache run the same part of the kernel together (fewer instruction-cache misses, at the
+     * price of waiting for the group's slowest warp).  Same results bit for bit.  With neither flag the
+     * library picks: on for scenes that march 1-8 objects without a distance BVH (measured on B200:
+     * C1 +29 %, C2 +6 %, C4 +5 %), off otherwise (spheres only -13 %, 65 marched objects -33 %).         */
+    OM_RENDER_PHASE_ALIGN = 1u << 7,
+    OM_RENDER_NO_PHASE_ALIGN = 1u << 8
 };
 
 typedef struct om_render_params {

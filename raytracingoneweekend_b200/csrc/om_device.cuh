@@ -36,9 +36,6 @@ constexpr int CTA_THREADS = 256;
 #define OM_RENDER_THREADS 1024  // one CTA per SM: one copy of the scene image, 32 warps (64 registers) to hide the
 #define OM_RENDER_MIN_CTAS 1    // instruction-cache misses of this 70 KB kernel: +23 % over 2 x 256 threads at 92 registers
 #endif
-#ifndef OM_PHASE_SYNC
-#define OM_PHASE_SYNC 0  // experiment: CTA-wide barriers between the traversal and the shading phase of k_render
-#endif
 constexpr int RENDER_THREADS = OM_RENDER_THREADS;  // k_render only
 
 using omk::RenderArgs;
@@ -56,7 +53,15 @@ struct Rng {
 // Inlined at a handful of draw sites that the warp reaches CONVERGED (see rng_take): the first
 // kernels called an out-of-line copy from every scalar draw, lane by lane, and spent 12 % of all
 // issued instructions there at 3.7 active lanes.
-__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
+#ifndef OM_PHILOX_INLINE
+#define OM_PHILOX_INLINE 1  // 0: one out-of-line copy shared by the draw sites (experiment)
+#endif
+#if OM_PHILOX_INLINE
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
     uint32_t c3 = 0u;  // STREAM_PATH
 #pragma unroll
     for (int r = 0; r < 10; r++) {
@@ -574,6 +579,20 @@ __device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& 
     return fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
 }
 
+// Phase alignment (OM_RENDER_PHASE_ALIGN): the 8 warps of one SM sub-partition (warp % 4; they share an L0 instruction
+// cache) meet at a named barrier at the top of the path loop and again between the closest-hit query and shading, so that
+// they stream the same part of this 70 KB kernel at the same time.  The count variant also tells the warps that ran out of
+// tickets when the last warp of their group has left the loop.
+constexpr int PB_GROUPS = 4;
+constexpr int PB_THREADS = RENDER_THREADS / PB_GROUPS;
+__device__ __forceinline__ unsigned phase_bar_id() { return 1u + ((threadIdx.x >> 5) % (unsigned)PB_GROUPS); }
+__device__ __forceinline__ int phase_bar_count(int pred) {
+    int r;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\tbar.red.popc.u32 %0, %1, %3, p;\n\t}" : "=r"(r) : "r"(phase_bar_id()), "r"(pred), "n"(PB_THREADS) : "memory");
+    return r;
+}
+__device__ __forceinline__ void phase_bar() { asm volatile("bar.sync %0, %1;" ::"r"(phase_bar_id()), "n"(PB_THREADS) : "memory"); }
+
 struct Hit {
     float t;
     uint32_t ref;  // REF_NONE = miss
@@ -908,6 +927,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
     const SceneHeader& S = A.scene;
     const bool brute = (A.flags & OM_RENDER_BRUTE_FORCE) != 0;
     const bool adaptive = (A.flags & OM_RENDER_ADAPTIVE) != 0;
+    const bool align = (A.flags & OM_RENDER_PHASE_ALIGN) != 0;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
     unsigned long long credited = 0, traced = 0;
     const uint32_t lane = threadIdx.x & 31u;
@@ -954,9 +974,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         bool fresh = true;
         while (__any_sync(FULL, todo > 0u)) {
             const bool alive = todo > 0u;
-#if OM_PHASE_SYNC
-            __syncthreads_count(1);
-#endif
+            if (align) phase_bar_count(1);
             if (alive && fresh) {
                 const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
                 rng_init(g, A.seed_lo, A.seed_hi, pxl, sample);
@@ -966,9 +984,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
                 fresh = false;
             }
             Hit h = closest_hit_warp<SMEM, COUNT, MA>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
-#if OM_PHASE_SYNC > 1
-            __syncthreads();
-#endif
+            if (align) phase_bar();
             if (alive) {
                 bool finished;
                 V3 result = color;
@@ -1005,14 +1021,10 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         }
     }
 
-#if OM_PHASE_SYNC
-    // out of tickets: keep answering the phase barriers until every warp of the CTA is out
-    while (__syncthreads_count(0) > 0) {
-#if OM_PHASE_SYNC > 1
-        __syncthreads();
-#endif
+    // out of tickets: keep answering the group's barriers until all of its warps are out
+    if (align) {
+        while (phase_bar_count(0) > 0) phase_bar();
     }
-#endif
     // ---- progress counters: warp-aggregate, one atomic per warp ----
     for (int o = 16; o > 0; o >>= 1) {
         credited += __shfl_xor_sync(FULL, credited, o);

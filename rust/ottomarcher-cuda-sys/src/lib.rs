@@ -19,6 +19,8 @@ pub const OM_RENDER_NO_SMEM_SCENE: u32 = 1 << 4;
 pub const OM_RENDER_COUNTERS: u32 = 1 << 5;
 pub const OM_RENDER_WAVEFRONT: u32 = 1 << 3;
 pub const OM_RENDER_PERSISTENT: u32 = 1 << 6;
+pub const OM_RENDER_PHASE_ALIGN: u32 = 1 << 7;
+pub const OM_RENDER_NO_PHASE_ALIGN: u32 = 1 << 8;
 pub const OM_FREEZE_NO_ALWAYS_LIST: u32 = 1 << 0;
 pub const OM_FREEZE_RAY_PADDING: u32 = 1 << 1;
 pub const OM_FREEZE_STATIC_PADDING: u32 = 1 << 2;

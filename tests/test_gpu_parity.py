@@ -358,6 +358,25 @@ def test_wavefront_equals_persistent_kernel_large(api, A, kind, seed):
     assert out[0][1:] == out[1][1:]
 
 
+@pytest.mark.parametrize("kind,seed,adaptive", [("random_scene", 1, False), ("random_scene", 1, True), ("marched", 3, False), ("rtiow_classic", 1, False)])
+def test_phase_alignment_changes_nothing(api, A, kind, seed, adaptive):
+    """OM_RENDER_PHASE_ALIGN only makes the warps of an SM sub-partition wait for each other (named barriers in
+    k_render); forced on, forced off and the library's own choice must give the same pixels and counters, also when
+    warps run out of tickets at different times (small image, adaptive retirement, a partition)."""
+    fz = api.FrozenHittableList.generate(kind, seed)
+    cam = cam_rtiow(api, 16 / 9)
+    base = A.RENDER_PERSISTENT | (A.RENDER_ADAPTIVE if adaptive else 0)
+    out = []
+    for fl in (A.RENDER_NO_PHASE_ALIGN, A.RENDER_PHASE_ALIGN, 0):
+        r = api.Renderer(fz, cam, api.render_params(320, 180, 12 if not adaptive else 40, seed=5, flags=base | fl))
+        r.launch(5); r.launch(0); r.sync()
+        out.append((r.read_pixels(), r.samples_done(), r.samples_traced()))
+        r.close()
+    for o in out[1:]:
+        assert_pixels_equal(out[0][0], o[0])
+        assert out[0][1:] == o[1:]
+
+
 def test_pipeline_flags_exclusive(api, A, rtiow):
     fz, _ = rtiow
     with pytest.raises(Exception):
