@@ -112,6 +112,39 @@ typedef struct om_marched_torus {
     om_material material;
 } om_marched_torus;
 
+/* `Arc<dyn Marched + Send + Sync>` as data (marched.rs:8-45; hits.rs:40,96-100,312-320,353-359): what a user
+ * type supplies to the trait — material(), to_local(), to_world(), to_world_f(), local_sdf() — with
+ * local_sdf written as a postfix program over f32 (one 32-bit word per instruction, opcode in the low 8
+ * bits, argument above; OM_SDF_CONST is followed by one word holding the f32 bits).  Operand stack of
+ * OM_SDF_STACK values, OM_SDF_REGS registers, every operation one IEEE f32 operation in the order written,
+ * so the device and the CPU oracle evaluate the same bits.  sdf() and get_outward_normal() are the trait's
+ * defaults (marched.rs:14-44): sdf(p) = to_world_f(local_sdf(to_local(p))), numeric normal with sign fix.   */
+enum {
+    OM_SDF_X = 1, OM_SDF_Y = 2, OM_SDF_Z = 3, /* push a component of the local point                     */
+    OM_SDF_CONST = 4,                          /* push the f32 whose bits are the next word              */
+    OM_SDF_ADD = 5, OM_SDF_SUB = 6, OM_SDF_MUL = 7, OM_SDF_DIV = 8, /* b = pop, a = pop, push a op b      */
+    OM_SDF_MIN = 9, OM_SDF_MAX = 10,           /* f32::min / f32::max                                    */
+    OM_SDF_NEG = 11, OM_SDF_ABS = 12, OM_SDF_SQRT = 13,
+    OM_SDF_LEN2 = 14, /* b = pop, a = pop, push sqrt(a*a + b*b + 0*0)       = Vec3(a,b,0).length()       */
+    OM_SDF_LEN3 = 15, /* c, b, a = pop x3, push sqrt(a*a + b*b + c*c)       = Vec3(a,b,c).length()       */
+    OM_SDF_STORE = 16, /* reg[arg] = pop                                                                 */
+    OM_SDF_LOAD = 17   /* push reg[arg]                                                                  */
+};
+#define OM_SDF_STACK 8
+#define OM_SDF_REGS 4
+#define OM_SDF_MAX_WORDS 256
+#define OM_SDF_INSN(op, arg) ((uint32_t)(op) | ((uint32_t)(arg) << 8))
+typedef struct om_dyn_marched {
+    float m_world_to_local[16]; /* to_local(p)  = this . p           (Mat4x4::dot, mat4x4.rs:45-48)       */
+    float m_local_to_world[16]; /* to_world(n)  = this . n           (applied to the local normal, w = 0) */
+    float world_f;              /* to_world_f(f) = f * world_f                                           */
+    /* Bounded::build_world_bounding_box (bounding_box.rs:69-73): a world box that contains every point
+     * with |sdf| < 0.005, or -INF/+INF = the trait's default "draw always".  Rays that miss the union of
+     * the marched objects' boxes skip the march (they could neither start nor end on a marched surface).  */
+    float bounds_lo[3], bounds_hi[3];
+    om_material material;
+} om_dyn_marched;
+
 /* camera.rs:9-29 Camera (all fields, same order)                                             */
 typedef struct om_camera {
     float origin[3];
@@ -145,7 +178,7 @@ typedef struct om_pixel {
 enum {
     OM_TYPE_SPHERE = 1, OM_TYPE_CUBE = 2, OM_TYPE_TRIANGLE = 3, OM_TYPE_INFINITE_PLANE = 4,
     OM_TYPE_PARALLELOGRAM = 5, OM_TYPE_MARCHED_SPHERE = 6, OM_TYPE_MARCHED_BOX = 7,
-    OM_TYPE_MARCHED_TORUS = 8
+    OM_TYPE_MARCHED_TORUS = 8, OM_TYPE_DYN_MARCHED = 9
 };
 #define OM_OBJ_ID(type, index) ((((uint64_t)(type)) << 32) | ((uint64_t)(index) + 1u))
 
@@ -228,8 +261,18 @@ OM_API om_status om_scene_add_parallelograms(om_scene* s, const om_barycentric* 
 OM_API om_status om_scene_add_marched_spheres(om_scene* s, const om_marched_sphere* a, size_t n);
 OM_API om_status om_scene_add_marched_boxes(om_scene* s, const om_marched_box* a, size_t n);
 OM_API om_status om_scene_add_marched_tori(om_scene* s, const om_marched_torus* a, size_t n);
-/* `world += Arc<dyn Traced>` / `Arc<dyn Marched>` (hits.rs:91-100): user trait objects cannot
- * cross to a device.  Always returns OM_ERR_UNSUPPORTED; present so the binding is total.     */
+/* `world += Arc<dyn Marched>` (hits.rs:96-100) for a user type described as data: one object and the
+ * n_words-word program of its local_sdf.  OM_ERR_INVALID for a malformed program (unknown opcode, stack
+ * under/overflow, register out of range or read before written, more than OM_SDF_MAX_WORDS words, result
+ * stack not exactly one value).  Dyn marched objects are scanned after the three typed marched lists, as
+ * in hits.rs:312-320; object id = OM_OBJ_ID(9, index).                                                  */
+OM_API om_status om_scene_add_dyn_marched(om_scene* s, const om_dyn_marched* obj, const uint32_t* code, size_t n_words);
+/* number of dyn marched objects, and a copy of object `index` with its program (code may be NULL to ask
+ * for *n_words only; on entry *n_words is the capacity of code).                                         */
+OM_API om_status om_scene_dyn_marched_count(const om_scene* s, uint64_t* count);
+OM_API om_status om_scene_get_dyn_marched(const om_scene* s, uint64_t index, om_dyn_marched* obj, uint32_t* code, size_t* n_words);
+/* `world += Arc<dyn Traced>` (hits.rs:91-95) and native trait objects in general: compiled host code
+ * cannot cross to a device.  Always returns OM_ERR_UNSUPPORTED; present so the binding is total.  */
 OM_API om_status om_scene_add_dyn_object(om_scene* s, const void* trait_object);
 /* counts per list, order: spheres,cubes,triangles,infinite_planes,parallelograms,
  * marched_spheres,marched_boxes,marched_tori */

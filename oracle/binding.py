@@ -40,6 +40,7 @@ def lib():
                     ("marched_spheres", A.MarchedSphere), ("marched_boxes", A.MarchedBox),
                     ("marched_tori", A.MarchedTorus)]:
         getattr(L, "omo_scene_add_" + name).argtypes = [vp, P(T), sz]
+    L.omo_scene_add_dyn_marched.argtypes = [vp, P(A.DynMarched), P(u32), sz]
     L.omo_scene_counts.argtypes = [vp, P(u64)]
     L.omo_scene_random.argtypes = [vp, u64]
     L.omo_scene_basic.argtypes = [vp]
@@ -124,6 +125,12 @@ class OracleScene:
         n = len(arr)
         if n:
             getattr(lib(), "omo_scene_add_" + kind)(self.h, arr, n)
+        return self
+
+    def add_dyn_marched(self, pod, code):
+        """One om_dyn_marched and its local_sdf program (list of u32 words)."""
+        arr = (C.c_uint32 * max(1, len(code)))(*code)
+        lib().omo_scene_add_dyn_marched(self.h, C.byref(pod), arr, len(code))
         return self
 
     def counts(self):

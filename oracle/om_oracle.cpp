@@ -113,6 +113,12 @@ OMO_API void omo_scene_add_parallelograms(omo_scene* s, const om_barycentric* a,
 OMO_API void omo_scene_add_marched_spheres(omo_scene* s, const om_marched_sphere* a, size_t n) { for (size_t i = 0; i < n; i++) s->w.marched_spheres.push_back(msphere_in(a[i])); }
 OMO_API void omo_scene_add_marched_boxes(omo_scene* s, const om_marched_box* a, size_t n) { for (size_t i = 0; i < n; i++) s->w.marched_boxes.push_back(mbox_in(a[i])); }
 OMO_API void omo_scene_add_marched_tori(omo_scene* s, const om_marched_torus* a, size_t n) { for (size_t i = 0; i < n; i++) s->w.marched_torus.push_back(mtorus_in(a[i])); }
+OMO_API void omo_scene_add_dyn_marched(omo_scene* s, const om_dyn_marched* a, const uint32_t* code, size_t n_words) {
+    DynMarched o;
+    o.m_world_to_local = Mat4x4::from_rows16(a->m_world_to_local); o.m_local_to_world = Mat4x4::from_rows16(a->m_local_to_world);
+    o.world_f = a->world_f; o.code.assign(code, code + n_words); o.material = mat_in(a->material);
+    s->w.marched_objects.push_back(o);
+}
 OMO_API void omo_scene_counts(const omo_scene* s, uint64_t c[8]) {
     c[0] = s->w.spheres.size(); c[1] = s->w.cubes.size(); c[2] = s->w.triangles.size(); c[3] = s->w.infinite_planes.size();
     c[4] = s->w.parallelograms.size(); c[5] = s->w.marched_spheres.size(); c[6] = s->w.marched_boxes.size(); c[7] = s->w.marched_torus.size();

@@ -11,6 +11,7 @@
 //    UNSTUCK_MAX_STEPS steps (never reached by any test scene).
 //  * random numbers come from ref::Rng (ref_rng.hpp) passed explicitly.
 #pragma once
+#include <cstring>
 #include <vector>
 
 #include "ref_math.hpp"
@@ -116,7 +117,7 @@ inline ScatterResult scatter(const Material& m, const Ray& r_in, const HitRecord
 
 // ---- object ids ----------------------------------------------------------------------------
 enum { T_SPHERE = 1, T_CUBE = 2, T_TRIANGLE = 3, T_INFINITE_PLANE = 4, T_PARALLELOGRAM = 5,
-       T_MARCHED_SPHERE = 6, T_MARCHED_BOX = 7, T_MARCHED_TORUS = 8 };
+       T_MARCHED_SPHERE = 6, T_MARCHED_BOX = 7, T_MARCHED_TORUS = 8, T_DYN_MARCHED = 9 };
 inline uint64_t make_id(uint32_t type, size_t index) { return ((uint64_t)type << 32) | (uint64_t)(index + 1); }
 
 // ---- traced.rs -----------------------------------------------------------------------------
@@ -339,6 +340,48 @@ struct MarchedTorus {  // marched.rs:104-151
     Vec3 get_outward_normal(const Vec3& p) const { return marched_outward_normal_default(*this, p); }
 };
 
+// A user's `impl Marched` handed over as data (include/ottomarcher.h, om_dyn_marched): stands for an element of
+// `marched_objects: Vec<Arc<dyn Marched + Send + Sync>>` (hits.rs:40).  The type supplies to_local / to_world /
+// to_world_f / local_sdf; sdf and the normal are the trait's defaults (marched.rs:14-44).  local_sdf is a postfix
+// program, one f32 operation per instruction in program order (opcodes: OM_SDF_* in the header).
+struct DynMarched {
+    Mat4x4 m_world_to_local, m_local_to_world;
+    float world_f;
+    std::vector<uint32_t> code;
+    Material material;
+    float local_sdf(const Vec3& p) const {
+        float st[8], reg[4] = {0.f, 0.f, 0.f, 0.f};
+        int sp = 0;
+        for (size_t pc = 0; pc < code.size(); pc++) {
+            const uint32_t op = code[pc] & 0xFFu, arg = code[pc] >> 8;
+            switch (op) {
+                case 1: st[sp++] = p.x(); break;
+                case 2: st[sp++] = p.y(); break;
+                case 3: st[sp++] = p.z(); break;
+                case 4: { pc++; float f; std::memcpy(&f, &code[pc], 4); st[sp++] = f; break; }
+                case 5: sp--; st[sp - 1] = st[sp - 1] + st[sp]; break;
+                case 6: sp--; st[sp - 1] = st[sp - 1] - st[sp]; break;
+                case 7: sp--; st[sp - 1] = st[sp - 1] * st[sp]; break;
+                case 8: sp--; st[sp - 1] = st[sp - 1] / st[sp]; break;
+                case 9: sp--; st[sp - 1] = fmin_(st[sp - 1], st[sp]); break;
+                case 10: sp--; st[sp - 1] = fmax_(st[sp - 1], st[sp]); break;
+                case 11: st[sp - 1] = -st[sp - 1]; break;
+                case 12: st[sp - 1] = std::fabs(st[sp - 1]); break;
+                case 13: st[sp - 1] = std::sqrt(st[sp - 1]); break;
+                case 14: sp--; st[sp - 1] = Vec3(st[sp - 1], st[sp], 0.f).length(); break;
+                case 15: sp -= 2; st[sp - 1] = Vec3(st[sp - 1], st[sp], st[sp + 1]).length(); break;
+                case 16: sp--; reg[arg & 3u] = st[sp]; break;
+                default: st[sp++] = reg[arg & 3u]; break;
+            }
+        }
+        return st[0];
+    }
+    Vec4 to_local(const Vec4& p) const { return m_world_to_local.dot(p); }
+    Vec4 to_world(const Vec4& p) const { return m_local_to_world.dot(p); }
+    float to_world_f(float f) const { return f * world_f; }
+    Vec3 get_outward_normal(const Vec3& p) const { return marched_outward_normal_default(*this, p); }
+};
+
 // ---- hits.rs -------------------------------------------------------------------------------
 constexpr float HIT_SIZE = 0.001f;  // hits.rs:113
 constexpr int UNSTUCK_MAX_STEPS = 1 << 20;
@@ -352,11 +395,13 @@ struct World {  // HittableList / FrozenHittableList, hits.rs:37-69 (no dyn list
     std::vector<MarchedSphere> marched_spheres;
     std::vector<MarchedBox> marched_boxes;
     std::vector<MarchedTorus> marched_torus;
+    std::vector<DynMarched> marched_objects;  // Vec<Arc<dyn Marched>>, scanned after the typed lists (hits.rs:312-320,353-359)
 
     // counters for the flop accounting of SURVEY.md §8(d); filled when non-null
     struct Counters { uint64_t segments = 0, traced_tests = 0, sdf_evals = 0, normal_evals = 0, march_steps = 0; };
 
-    bool has_marched() const { return !marched_spheres.empty() || !marched_boxes.empty() || !marched_torus.empty(); }
+    bool has_marched() const { return !marched_spheres.empty() || !marched_boxes.empty() || !marched_torus.empty() || !marched_objects.empty(); }
+    size_t n_marched() const { return marched_spheres.size() + marched_boxes.size() + marched_torus.size() + marched_objects.size(); }
 
     // hits.rs:336-365
     float unstuck(float t, const Ray& r, Counters* cn) const {
@@ -368,14 +413,15 @@ struct World {  // HittableList / FrozenHittableList, hits.rs:37-69 (no dyn list
         for (size_t i = 0; i < marched_spheres.size(); i++) { float nd = std::fabs(marched_sdf(marched_spheres[i], p)); if (nd < d) { d = nd; kind = 0; which = i; } }
         for (size_t i = 0; i < marched_boxes.size(); i++)   { float nd = std::fabs(marched_sdf(marched_boxes[i], p));   if (nd < d) { d = nd; kind = 1; which = i; } }
         for (size_t i = 0; i < marched_torus.size(); i++)   { float nd = std::fabs(marched_sdf(marched_torus[i], p));   if (nd < d) { d = nd; kind = 2; which = i; } }
-        if (cn) cn->sdf_evals += marched_spheres.size() + marched_boxes.size() + marched_torus.size();
+        for (size_t i = 0; i < marched_objects.size(); i++) { float nd = std::fabs(marched_sdf(marched_objects[i], p)); if (nd < d) { d = nd; kind = 3; which = i; } }
+        if (cn) cn->sdf_evals += n_marched();
         float aux = d;
         if (kind < 0) return INF;
         int steps = 0;
         while (aux < HIT_SIZE && steps < UNSTUCK_MAX_STEPS) {
             new_t += MIN_STEP_SIZE;
             Vec3 q = r.at(new_t);
-            aux = std::fabs(kind == 0 ? marched_sdf(marched_spheres[which], q) : kind == 1 ? marched_sdf(marched_boxes[which], q) : marched_sdf(marched_torus[which], q));
+            aux = std::fabs(kind == 0 ? marched_sdf(marched_spheres[which], q) : kind == 1 ? marched_sdf(marched_boxes[which], q) : kind == 2 ? marched_sdf(marched_torus[which], q) : marched_sdf(marched_objects[which], q));
             steps++;
             if (cn) cn->sdf_evals++;
         }
@@ -419,7 +465,12 @@ struct World {  // HittableList / FrozenHittableList, hits.rs:37-69 (no dyn list
                 float d = std::fabs(marched_sdf(o, point));
                 if (d < distance) { distance = d; normal = o.get_outward_normal(point); material = &o.material; id = make_id(T_MARCHED_TORUS, i); if (cn) cn->normal_evals++; }
             }
-            if (cn) { cn->march_steps++; cn->sdf_evals += marched_spheres.size() + marched_boxes.size() + marched_torus.size(); }
+            for (size_t i = 0; i < marched_objects.size(); i++) {
+                const DynMarched& o = marched_objects[i];
+                float d = std::fabs(marched_sdf(o, point));
+                if (d < distance) { distance = d; normal = o.get_outward_normal(point); material = &o.material; id = make_id(T_DYN_MARCHED, i); if (cn) cn->normal_evals++; }
+            }
+            if (cn) { cn->march_steps++; cn->sdf_evals += n_marched(); }
             if (!material) return have;
             if (distance < HIT_SIZE) {
                 rec.t = t; rec.point = point; rec.normal = normal; rec.material = *material; rec.obj_id = id;

@@ -77,6 +77,18 @@ class MarchedTorus(C.Structure):
                 ("material", Material)]
 
 
+class DynMarched(C.Structure):  # om_dyn_marched: Arc<dyn Marched> as data
+    _fields_ = [("m_world_to_local", f32 * 16), ("m_local_to_world", f32 * 16), ("world_f", f32),
+                ("bounds_lo", f32 * 3), ("bounds_hi", f32 * 3), ("material", Material)]
+
+
+# local_sdf program opcodes (OM_SDF_*)
+SDF_OPS = {"x": 1, "y": 2, "z": 3, "const": 4, "add": 5, "sub": 6, "mul": 7, "div": 8, "min": 9, "max": 10, "neg": 11, "abs": 12,
+           "sqrt": 13, "len2": 14, "len3": 15, "store": 16, "load": 17}
+SDF_STACK, SDF_REGS, SDF_MAX_WORDS = 8, 4, 256
+TYPE_DYN_MARCHED = 9
+
+
 class Camera(C.Structure):
     _fields_ = [("origin", f32 * 3), ("horizontal", f32 * 3), ("vertical", f32 * 3), ("lower_left_corner", f32 * 3),
                 ("u_of_plane", f32 * 3), ("v_of_plane", f32 * 3), ("w_of_plane", f32 * 3), ("lens_radius", f32),
@@ -98,6 +110,7 @@ assert C.sizeof(Material) == 24
 assert C.sizeof(Sphere) == 152
 assert C.sizeof(Pixel) == 40
 assert C.sizeof(Camera) == 104
+assert C.sizeof(DynMarched) == 180
 
 # numpy view of om_pixel (same layout) for vectorised test/bench code
 PIXEL_DTYPE = [("sum", "<f4", (3,)), ("n", "<u4"), ("avg_depth", "<f4"), ("bad_avgs", "<u4"), ("bloom", "<u8"),

@@ -152,6 +152,32 @@ class MarchedTorus:
         s = A.MarchedTorus(); _lib.load().om_marched_torus_new(C.byref(s), m_local_to_world.e, _f3(local_sizes), C.byref(mat)); return s
 
 
+def sdf_program(tokens):
+    """Assemble a local_sdf program (include/ottomarcher.h, OM_SDF_*): tokens are "x" "y" "z", a number (pushed as an
+    f32 constant), "add" "sub" "mul" "div" "min" "max" "neg" "abs" "sqrt" "len2" "len3", ("store", r), ("load", r)."""
+    import struct
+    words = []
+    for t in tokens:
+        if isinstance(t, (int, float)):
+            words += [A.SDF_OPS["const"], struct.unpack("<I", struct.pack("<f", float(t)))[0]]
+        elif isinstance(t, tuple):
+            words.append(A.SDF_OPS[t[0]] | (int(t[1]) << 8))
+        else:
+            words.append(A.SDF_OPS[t])
+    return words
+
+
+class DynMarched:
+    """A user's `impl Marched` (marched.rs:8-45) as data: `world += Arc::new(obj) as Arc<dyn Marched + Send + Sync>`
+    (hits.rs:96-100).  to_local / to_world are matrices, to_world_f a factor, local_sdf a program (sdf_program)."""
+
+    def __init__(self, m_world_to_local, m_local_to_world, world_f, code, material, bounds=None):
+        inf = float("inf")
+        lo, hi = bounds if bounds is not None else ((-inf,) * 3, (inf,) * 3)
+        self.pod = A.DynMarched(m_world_to_local.e, m_local_to_world.e, world_f, _f3(lo), _f3(hi), material)
+        self.code = [int(w) for w in code]
+
+
 class Camera:
     @staticmethod
     def new(lookfrom, lookat, vup, vfov_in_degrees, aspect_ratio, aperture, focus_dist):
@@ -177,6 +203,7 @@ class HittableList:
 
     def __init__(self):
         self.lists = {k: [] for k in _LISTS}
+        self.dyn_marched = []  # marched_objects: Vec<Arc<dyn Marched>> (DynMarched)
         self._generated = []  # (kind, seed, n) requests replayed into the C scene
 
     def clear(self):
@@ -187,8 +214,10 @@ class HittableList:
             self.lists[obj.kind].append(obj.pod)
         elif type(obj) in _KIND_OF:
             self.lists[_KIND_OF[type(obj)]].append(obj)
+        elif isinstance(obj, DynMarched):
+            self.dyn_marched.append(obj)
         else:
-            # Arc<dyn Traced>/Arc<dyn Marched>: the ABI reports OM_ERR_UNSUPPORTED
+            # native trait objects (Arc<dyn Traced>, compiled Marched impls): the ABI reports OM_ERR_UNSUPPORTED
             h = C.c_void_p()
             _lib.call("om_scene_create", C.byref(h))
             try:
@@ -210,6 +239,9 @@ class HittableList:
         for k, arr in self.arrays().items():
             if arr is not None:
                 _lib.call("om_scene_add_" + k, s.h, arr, len(arr))
+        for d in self.dyn_marched:
+            code = (C.c_uint32 * max(1, len(d.code)))(*d.code)
+            _lib.call("om_scene_add_dyn_marched", s.h, C.byref(d.pod), code, len(d.code))
         _lib.call("om_scene_freeze", s.h, C.byref(cam) if cam is not None else None, flags)
         return s
 
@@ -247,6 +279,17 @@ class FrozenHittableList:
             arr = (types[i] * n)()
             _lib.call("om_scene_get_list", self.h, i, arr, C.sizeof(arr))
             out[name] = arr
+        return out
+
+    def dyn_marched(self):
+        """[(om_dyn_marched, program words)] in list order."""
+        n = C.c_uint64()
+        _lib.call("om_scene_dyn_marched_count", self.h, C.byref(n))
+        out = []
+        for i in range(n.value):
+            pod, code, nw = A.DynMarched(), (C.c_uint32 * A.SDF_MAX_WORDS)(), C.c_size_t(A.SDF_MAX_WORDS)
+            _lib.call("om_scene_get_dyn_marched", self.h, i, C.byref(pod), code, C.byref(nw))
+            out.append((pod, list(code[:nw.value])))
         return out
 
     def stats(self):

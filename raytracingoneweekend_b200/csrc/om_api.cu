@@ -150,8 +150,39 @@ OM_ADD(om_scene_add_parallelograms, om_barycentric, parallelograms)
 OM_ADD(om_scene_add_marched_spheres, om_marched_sphere, marched_spheres)
 OM_ADD(om_scene_add_marched_boxes, om_marched_box, marched_boxes)
 OM_ADD(om_scene_add_marched_tori, om_marched_torus, marched_tori)
+om_status om_scene_add_dyn_marched(om_scene* s, const om_dyn_marched* obj, const uint32_t* code, size_t n_words) {
+    if (!s || !obj || !code) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: NULL argument");
+    if (s->frozen) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: scene is frozen (om_scene_clear first)");
+    const char* why = omh::check_sdf_program(code, n_words);
+    if (why[0]) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: %s", why);
+    omh::SceneLists& L = s->lists;
+    if (L.dyn_marched.size() + 1 > 0x0FFFFFFFull || L.dyn_code.size() + n_words > 0x3FFFFFFFull) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: too many objects");
+    if (L.dyn_code_first.empty()) L.dyn_code_first.push_back(0u);
+    L.dyn_marched.push_back(*obj);
+    L.dyn_code.insert(L.dyn_code.end(), code, code + n_words);
+    L.dyn_code_first.push_back(uint32_t(L.dyn_code.size()));
+    return OM_OK;
+}
+om_status om_scene_dyn_marched_count(const om_scene* s, uint64_t* count) {
+    if (!s || !count) return fail(OM_ERR_INVALID, "om_scene_dyn_marched_count: NULL argument");
+    *count = s->lists.dyn_marched.size();
+    return OM_OK;
+}
+om_status om_scene_get_dyn_marched(const om_scene* s, uint64_t index, om_dyn_marched* obj, uint32_t* code, size_t* n_words) {
+    if (!s || !n_words) return fail(OM_ERR_INVALID, "om_scene_get_dyn_marched: NULL argument");
+    const omh::SceneLists& L = s->lists;
+    if (index >= L.dyn_marched.size()) return fail(OM_ERR_INVALID, "om_scene_get_dyn_marched: object %llu does not exist", (unsigned long long)index);
+    const size_t first = L.dyn_code_first[index], n = L.dyn_code_first[index + 1] - first;
+    if (obj) *obj = L.dyn_marched[index];
+    if (code) {
+        if (*n_words < n) return fail(OM_ERR_INVALID, "om_scene_get_dyn_marched: room for %zu words, program has %zu", *n_words, n);
+        memcpy(code, L.dyn_code.data() + first, n * sizeof(uint32_t));
+    }
+    *n_words = n;
+    return OM_OK;
+}
 om_status om_scene_add_dyn_object(om_scene*, const void*) {
-    return fail(OM_ERR_UNSUPPORTED, "Arc<dyn Traced>/Arc<dyn Marched> objects (hits.rs:91-100) cannot cross to the device");
+    return fail(OM_ERR_UNSUPPORTED, "native Arc<dyn Traced>/Arc<dyn Marched> objects (hits.rs:91-100) cannot cross to the device; describe a Marched type as data with om_scene_add_dyn_marched");
 }
 om_status om_scene_counts(const om_scene* s, uint64_t c[8]) {
     if (!s || !c) return fail(OM_ERR_INVALID, "om_scene_counts: NULL argument");

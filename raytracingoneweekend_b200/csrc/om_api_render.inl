@@ -441,7 +441,7 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
         if (!(p.flags & (OM_RENDER_PHASE_ALIGN | OM_RENDER_NO_PHASE_ALIGN))) {  // automatic choice (see OM_RENDER_PHASE_ALIGN)
             const omd::SceneHeader& sh = r->scene->fz.hdr;
             const bool accel = (sh.mgrid_dim[0] | sh.n_mbvh_nodes) != 0u;
-            if (sh.n_marched >= 1u && sh.n_marched <= 8u && !accel) r->p.flags |= OM_RENDER_PHASE_ALIGN;
+            if (sh.n_marched >= 1u && sh.n_marched <= 8u && !accel && sh.n[omd::PT_MDYN] == 0u) r->p.flags |= OM_RENDER_PHASE_ALIGN;
         }
         if (r->p.flags & OM_RENDER_NO_PHASE_ALIGN) r->p.flags &= ~(uint32_t)OM_RENDER_PHASE_ALIGN;
         if (r->p.flags & OM_RENDER_WAVEFRONT) {

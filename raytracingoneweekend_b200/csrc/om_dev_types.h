@@ -5,7 +5,8 @@
 //  hot image  (staged into shared memory by TMA bulk copy when it fits; else read from global/L2)
 //      BVH nodes 64 B | sphere world->local rows 48 B | cube world->local rows 48 B |
 //      triangle 64 B | infinite plane 32 B | parallelogram 64 B | always-test refs 4 B |
-//      marched sphere 16 B | marched box 32 B | marched torus 144 B | sphere material type 1 B
+//      marched sphere 16 B | marched box 32 B | marched torus 144 B | dyn marched 112 B + its program, 4 B per word |
+//      sphere material type 1 B
 //  cold image (global memory; touched once per hit, not per test)
 //      sphere local->world rows 48 B | cube local->world rows 48 B | material+bloom 32 B per object
 #pragma once
@@ -16,7 +17,8 @@ namespace omd {
 // primitive type codes in the reference's scan order (hits.rs:370-371): on equal t the LATER
 // object of the linear scan wins (`root > t_max` rejects only strictly larger roots,
 // traced.rs:51,108,178,282), so a larger ref beats a smaller one.
-enum : uint32_t { PT_SPHERE = 0, PT_CUBE = 1, PT_TRI = 2, PT_PLANE = 3, PT_PARA = 4, PT_MSPHERE = 5, PT_MBOX = 6, PT_MTORUS = 7 };
+enum : uint32_t { PT_SPHERE = 0, PT_CUBE = 1, PT_TRI = 2, PT_PLANE = 3, PT_PARA = 4, PT_MSPHERE = 5, PT_MBOX = 6, PT_MTORUS = 7, PT_MDYN = 8 };
+constexpr uint32_t PT_COUNT = 9;
 constexpr uint32_t REF_NONE = 0xFFFFFFFFu;
 #if defined(__CUDACC__)
 #define OMD_HD __host__ __device__ __forceinline__
@@ -28,20 +30,20 @@ OMD_HD uint32_t ref_type(uint32_t ref) { return ref >> 28; }
 OMD_HD uint32_t ref_index(uint32_t ref) { return ref & 0x0FFFFFFFu; }
 
 // sizes in 16-byte units
-constexpr uint32_t U_NODE = 4, U_XF = 3, U_BARY = 4, U_PLANE = 2, U_MSPHERE = 1, U_MBOX = 2, U_MTORUS = 9, U_MAT = 2;
+constexpr uint32_t U_NODE = 4, U_XF = 3, U_BARY = 4, U_PLANE = 2, U_MSPHERE = 1, U_MBOX = 2, U_MTORUS = 9, U_MDYN = 7, U_MAT = 2;
 
 struct SceneHeader {
-    uint32_t n[8];         // object count per PT_* type
+    uint32_t n[PT_COUNT];  // object count per PT_* type
     uint32_t n_nodes;      // BVH inner nodes (0 = no BVH primitives)
     uint32_t n_large;      // refs in the always-test list (infinite planes, scene-sized objects)
     uint32_t n_bvh_prims;  // primitives reachable through the BVH
     uint32_t bvh_depth;
     // hot image offsets, 16-byte units
-    uint32_t off_nodes, off_hot[8], off_large;
+    uint32_t off_nodes, off_hot[PT_COUNT], off_large;
     uint32_t hot_units;    // total size of the hot image
     // cold image offsets, 16-byte units
     uint32_t off_sph_l2w, off_cube_l2w, off_mat;
-    uint32_t mat_base[8];  // first material record of each type
+    uint32_t mat_base[PT_COUNT];  // first material record of each type
     uint32_t cold_units;
     // padded union of the marched objects' bounds: a ray that misses it cannot hit a marched
     // object and cannot start inside one.  lo > hi when the scene has no marched object.
@@ -62,6 +64,9 @@ struct SceneHeader {
     // != 0: the BVH boxes carry only the distance-independent padding; the traversal widens each box by
     // dyn_pad * (largest distance from the ray origin to a point of the box), see om_scene.cpp
     float dyn_pad;
+    // dyn marched object i (PT_MDYN): world->local rows 0-2, local->world rows 0-2, {world_f, first word, word count, 0};
+    // the programs' words, 4 per unit, start at off_dyn_code
+    uint32_t off_dyn_code;
     uint32_t off_sph_mat;  // hot image: one byte per sphere = its material type (shade class of a hit, om_wavefront.cuh)
 };
 

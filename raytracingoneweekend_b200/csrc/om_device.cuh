@@ -131,6 +131,10 @@ struct SceneView {
         return __ldg(hot_g + u);
     }
     __device__ __forceinline__ float4 cold(uint32_t u) const { return __ldg(cold_g + u); }
+    __device__ __forceinline__ uint32_t hot_word(uint32_t u, uint32_t i) const {  // 32-bit word i of the section starting at unit u
+        if (SMEM) return reinterpret_cast<const uint32_t*>(om_smem + u)[i];
+        return __ldg(reinterpret_cast<const uint32_t*>(hot_g + u) + i);
+    }
     __device__ __forceinline__ uint32_t hot_byte(uint32_t u, uint32_t i) const {  // byte i of the section starting at unit u
         if (SMEM) return reinterpret_cast<const uint8_t*>(om_smem + u)[i];
         return __ldg(reinterpret_cast<const uint8_t*>(hot_g + u) + i);
@@ -412,7 +416,58 @@ __device__ __forceinline__ V3 torus_to_local(const SceneView<SMEM>& sv, uint32_t
     const float qx = p.x * si.x, qy = p.y * si.y, qz = p.z * si.z, qw = 1.f * si.w;
     return v3(r0.x * qx + r0.y * qy + r0.z * qz + r0.w * qw, r1.x * qx + r1.y * qy + r1.z * qz + r1.w * qw, r2.x * qx + r2.y * qy + r2.z * qz + r2.w * qw);
 }
+// local_sdf of a dyn marched object (om_dyn_marched, include/ottomarcher.h): the postfix program at words
+// [first, first + len) of the code pool, evaluated at local point p.  One f32 operation per instruction, in program
+// order; the host has checked the program (omh::check_sdf_program), so there are no bounds tests here.
 template <bool SMEM>
+__device__ __noinline__ float sdf_program(SceneView<SMEM> sv, uint32_t off_code, uint32_t first, uint32_t len, V3 p) {
+    float st[OM_SDF_STACK], reg[OM_SDF_REGS];
+    int sp = 0;
+    for (uint32_t pc = first; pc < first + len; pc++) {
+        const uint32_t w = sv.hot_word(off_code, pc), op = w & 0xFFu, arg = w >> 8;
+        switch (op) {
+            case OM_SDF_X: st[sp++] = p.x; break;
+            case OM_SDF_Y: st[sp++] = p.y; break;
+            case OM_SDF_Z: st[sp++] = p.z; break;
+            case OM_SDF_CONST: pc++; st[sp++] = __uint_as_float(sv.hot_word(off_code, pc)); break;
+            case OM_SDF_ADD: sp--; st[sp - 1] = st[sp - 1] + st[sp]; break;
+            case OM_SDF_SUB: sp--; st[sp - 1] = st[sp - 1] - st[sp]; break;
+            case OM_SDF_MUL: sp--; st[sp - 1] = st[sp - 1] * st[sp]; break;
+            case OM_SDF_DIV: sp--; st[sp - 1] = st[sp - 1] / st[sp]; break;
+            case OM_SDF_MIN: sp--; st[sp - 1] = fminf(st[sp - 1], st[sp]); break;
+            case OM_SDF_MAX: sp--; st[sp - 1] = fmaxf(st[sp - 1], st[sp]); break;
+            case OM_SDF_NEG: st[sp - 1] = -st[sp - 1]; break;
+            case OM_SDF_ABS: st[sp - 1] = fabsf(st[sp - 1]); break;
+            case OM_SDF_SQRT: st[sp - 1] = sqrtf(st[sp - 1]); break;
+            case OM_SDF_LEN2: sp--; st[sp - 1] = om::length(v3(st[sp - 1], st[sp], 0.f)); break;
+            case OM_SDF_LEN3: sp -= 2; st[sp - 1] = om::length(v3(st[sp - 1], st[sp], st[sp + 1])); break;
+            case OM_SDF_STORE: sp--; reg[arg & (OM_SDF_REGS - 1)] = st[sp]; break;
+            default: st[sp++] = reg[arg & (OM_SDF_REGS - 1)]; break;  // OM_SDF_LOAD
+        }
+    }
+    return st[0];
+}
+struct DynObj {  // hot record of a dyn marched object
+    float4 w2l0, w2l1, w2l2;
+    float world_f;
+    uint32_t first, len;
+};
+template <bool SMEM>
+__device__ __forceinline__ DynObj load_dyn(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t i) {
+    const uint32_t u = S.off_hot[omd::PT_MDYN] + omd::U_MDYN * i;
+    DynObj d;
+    d.w2l0 = sv.hot(u); d.w2l1 = sv.hot(u + 1); d.w2l2 = sv.hot(u + 2);
+    const float4 m = sv.hot(u + 6);
+    d.world_f = m.x; d.first = __float_as_uint(m.y); d.len = __float_as_uint(m.z);
+    return d;
+}
+// Mat4x4::dot of a point (w = 1): x*x + y*y + z*z + w*1 (mat4x4.rs:45-48, vec4.rs dot)
+__device__ __forceinline__ V3 xf_point_w1(float4 r0, float4 r1, float4 r2, V3 p) {
+    return v3(r0.x * p.x + r0.y * p.y + r0.z * p.z + r0.w * 1.f, r1.x * p.x + r1.y * p.y + r1.z * p.z + r1.w * 1.f, r2.x * p.x + r2.y * p.y + r2.z * p.z + r2.w * 1.f);
+}
+// DYN: the scene may hold dyn marched objects.  The kernel that renders scenes without marched structures and without dyn
+// objects (k_render<.., MA = 0 or 1>) is instantiated with DYN = false and contains none of this code (see march()).
+template <bool SMEM, bool DYN>
 __device__ __forceinline__ float marched_sdf(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t type, uint32_t i, V3 p) {
     if (type == omd::PT_MSPHERE) {
         const float4 cr = sv.hot(S.off_hot[omd::PT_MSPHERE] + omd::U_MSPHERE * i);
@@ -421,10 +476,13 @@ __device__ __forceinline__ float marched_sdf(const SceneView<SMEM>& sv, const Sc
         const uint32_t u = S.off_hot[omd::PT_MBOX] + omd::U_MBOX * i;
         const float4 c = sv.hot(u), s = sv.hot(u + 1);
         return box_local_sdf(p - v3(c.x, c.y, c.z), v3(s.x, s.y, s.z));
-    } else {
+    } else if (!DYN || type == omd::PT_MTORUS) {
         const uint32_t u = S.off_hot[omd::PT_MTORUS] + omd::U_MTORUS * i;
         const float4 sz = sv.hot(u + 8);
         return torus_local_sdf(torus_to_local(sv, u, p), sz.x, sz.y) * sz.z;  // to_world_f marched.rs:148-150
+    } else {  // trait default, marched.rs:14-18
+        const DynObj d = load_dyn(sv, S, i);
+        return sdf_program(sv, S.off_dyn_code, d.first, d.len, xf_point_w1(d.w2l0, d.w2l1, d.w2l2, p)) * d.world_f;
     }
 }
 
@@ -446,7 +504,7 @@ __device__ __forceinline__ V3 numeric_local_normal(V3 p, LSDF lsdf) {
 }
 // Marched::get_outward_normal (marched.rs:19-24; MarchedSphere override :60-63).  Out of line: it
 // runs once per marched HIT, not per step (see march()).
-template <bool SMEM>
+template <bool SMEM, bool DYN>
 __device__ __noinline__ V3 marched_normal(SceneView<SMEM> sv, const SceneHeader& S, uint32_t ref, V3 p) {
     const uint32_t type = omd::ref_type(ref), i = omd::ref_index(ref);
     if (type == omd::PT_MSPHERE) {
@@ -459,22 +517,32 @@ __device__ __noinline__ V3 marched_normal(SceneView<SMEM> sv, const SceneHeader&
         const V3 n = numeric_local_normal(p - v3(c.x, c.y, c.z), [&](V3 q) { return box_local_sdf(q, sizes); });
         // to_world of a vector: n + n.w * center with n.w = 0 (marched.rs:96-98)
         return om::unit(v3(n.x + 0.f * c.x, n.y + 0.f * c.y, n.z + 0.f * c.z));
-    } else {
+    } else if (!DYN || type == omd::PT_MTORUS) {
         const uint32_t u = S.off_hot[omd::PT_MTORUS] + omd::U_MTORUS * i;
         const float4 sz = sv.hot(u + 8);
         const V3 n = numeric_local_normal(torus_to_local(sv, u, p), [&](V3 q) { return torus_local_sdf(q, sz.x, sz.y); });
         const float4 r0 = sv.hot(u + 3), r1 = sv.hot(u + 4), r2 = sv.hot(u + 5), sc = sv.hot(u + 7);
         const V3 w = xf_vec(r0, r1, r2, n);  // L2W_TR . (n, 0)
         return om::unit(v3(w.x * sc.x, w.y * sc.y, w.z * sc.z));
+    } else {  // trait defaults, marched.rs:19-44
+        const DynObj d = load_dyn(sv, S, i);
+        const V3 n = numeric_local_normal(xf_point_w1(d.w2l0, d.w2l1, d.w2l2, p), [&](V3 q) { return sdf_program(sv, S.off_dyn_code, d.first, d.len, q); });
+        const uint32_t u = S.off_hot[omd::PT_MDYN] + omd::U_MDYN * i;
+        const float4 r0 = sv.hot(u + 3), r1 = sv.hot(u + 4), r2 = sv.hot(u + 5);
+        // to_world(n, 0): x*x + y*y + z*z + w*0
+        return om::unit(v3(r0.x * n.x + r0.y * n.y + r0.z * n.z + r0.w * 0.f, r1.x * n.x + r1.y * n.y + r1.z * n.z + r1.w * 0.f, r2.x * n.x + r2.y * n.y + r2.z * n.z + r2.w * 0.f));
     }
 }
 
 // j-th marched object in the reference's order: spheres, boxes, tori (hits.rs:301-311)
+template <bool DYN = true>
 __device__ __forceinline__ uint32_t marched_ref(const SceneHeader& S, uint32_t j) {
     const uint32_t n_ms = S.n[omd::PT_MSPHERE], n_mb = S.n[omd::PT_MBOX];
     if (j < n_ms) return omd::make_ref(omd::PT_MSPHERE, j);
     if (j < n_ms + n_mb) return omd::make_ref(omd::PT_MBOX, j - n_ms);
-    return omd::make_ref(omd::PT_MTORUS, j - n_ms - n_mb);
+    const uint32_t n_mt = S.n[omd::PT_MTORUS];
+    if (!DYN || j < n_ms + n_mb + n_mt) return omd::make_ref(omd::PT_MTORUS, j - n_ms - n_mb);
+    return omd::make_ref(omd::PT_MDYN, j - n_ms - n_mb - n_mt);  // marched_objects, after the typed lists (hits.rs:312-320)
 }
 constexpr int MSTACK = 40;  // scratch entries nearest_marched needs (<= STACK_DEPTH: the traversal stack is free by then)
 struct Near {
@@ -482,7 +550,7 @@ struct Near {
     float d;       // min over the marched objects of |sdf(p)|
     uint32_t ref;  // the first object that attains it (strict `<`, hits.rs:304,345); REF_NONE if none
 };
-template <bool SMEM>
+template <bool SMEM, bool DYN>
 __device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p);
 // min_j |sdf_j(p)| with help of the host-built structures (scenes with many marched objects):
 //  - inside the candidate grid only the cell's list is evaluated, in the reference's order: the objects left out are
@@ -491,7 +559,8 @@ __device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHead
 //    a LOWER bound of every |sdf| in it is strictly above that minimum, so what is skipped can neither be the minimum nor
 //    tie with it; the tree hands objects out of order, so an equal value from a smaller index takes over — the first
 //    object of the reference's scan that attains the minimum (om_scene.cpp, build_marched_bvh).
-// When the walk runs out of scratch stack it scans every object instead.
+// When the walk runs out of scratch stack it scans every object instead.  (Scenes with dyn marched objects have neither
+// structure - a user program has no analytic bounds - so this code never meets one.)
 template <bool SMEM>
 __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const SceneHeader& S, V3 p, int2* stk) {
     Near n;
@@ -511,8 +580,8 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
             const uint32_t first = __float_as_uint((cell & 1u) ? cc.z : cc.x), count = __float_as_uint((cell & 1u) ? cc.w : cc.y);
             n.evals = count;
             for (uint32_t k = first; k < first + count; k++) {
-                const uint32_t ref = marched_ref(S, word(S.off_mgrid_lists, k));
-                const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+                const uint32_t ref = marched_ref<false>(S, word(S.off_mgrid_lists, k));
+                const float d = fabsf(marched_sdf<SMEM, false>(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
                 if (d < n.d) { n.d = d; n.ref = ref; }
             }
             return n;
@@ -548,22 +617,22 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
         }
         if (!walk) break;
         if (j == 0xFFFFFFFFu) return n;
-        const uint32_t ref = marched_ref(S, j);
-        const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+        const uint32_t ref = marched_ref<false>(S, j);
+        const float d = fabsf(marched_sdf<SMEM, false>(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
         n.evals++;
         if (d < n.d || (d == n.d && j < best_j && best_j != 0xFFFFFFFFu)) { n.d = d; n.ref = ref; best_j = j; }
     }
-    return nearest_marched(sv, S, p);
+    return nearest_marched<SMEM, false>(sv, S, p);
 }
-template <bool SMEM>
-__device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p) {  // hits.rs:301-311
+template <bool SMEM, bool DYN>
+__device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHeader& S, V3 p) {  // hits.rs:301-320
     Near n;
     n.d = kInf;
     n.ref = omd::REF_NONE;
     n.evals = S.n_marched;
     for (uint32_t j = 0; j < S.n_marched; j++) {
-        const uint32_t ref = marched_ref(S, j);
-        const float d = fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+        const uint32_t ref = marched_ref<DYN>(S, j);
+        const float d = fabsf(marched_sdf<SMEM, DYN>(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
         if (d < n.d) { n.d = d; n.ref = ref; }
     }
     return n;
@@ -572,11 +641,11 @@ __device__ __noinline__ Near nearest_marched(SceneView<SMEM> sv, const SceneHead
 template <bool SMEM>
 __device__ __forceinline__ Near nearest_marched(const SceneView<SMEM>& sv, const SceneHeader& S, V3 p, int2* stk) {  // stk: MSTACK entries of scratch
     if ((S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u) return nearest_marched_accel(sv, S, p, stk);
-    return nearest_marched(sv, S, p);
+    return nearest_marched<SMEM, true>(sv, S, p);
 }
-template <bool SMEM>
+template <bool SMEM, bool DYN = true>
 __device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& S, uint32_t ref, V3 p) {
-    return fabsf(marched_sdf(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
+    return fabsf(marched_sdf<SMEM, DYN>(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
 }
 
 // Phase alignment (OM_RENDER_PHASE_ALIGN): the 8 warps of one SM sub-partition (warp % 4; they share an L0 instruction
@@ -602,10 +671,10 @@ struct Hit {
 // FrozenHittableList::hit, marched part (hits.rs:288-332) + unstuck (hits.rs:336-365).
 // `closest` is the traced hit distance (or t_max).  Returns ref == REF_NONE when the march ends
 // without a hit (the traced record stands).
-// ACCEL: the scene has a candidate grid / distance BVH.  k_render is instantiated for either case (template MA) and the host
+// ACCEL: the scene has a candidate grid / distance BVH.  DYN: it has dyn marched objects (om_dyn_marched).  k_render is instantiated for either case (template MA) and the host
 // picks: merely linking the structures' code into the kernel that renders C2 (one marched torus, never uses them) cost it
 // 8-10 % (more spill traffic in the 64-register main body), so that kernel does not contain it.
-template <bool SMEM, bool COUNT, bool ACCEL>
+template <bool SMEM, bool COUNT, bool ACCEL, bool DYN>
 __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, Counters* cn, int2* stk) {
     Hit out;
     out.t = closest;
@@ -618,14 +687,14 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
     {
         const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
         float new_t = t_min;
-        const Near n0 = ACCEL ? nearest_marched_accel(sv, S, ray_at(r, t_min), stk) : nearest_marched(sv, S, ray_at(r, t_min));
+        const Near n0 = ACCEL ? nearest_marched_accel(sv, S, ray_at(r, t_min), stk) : nearest_marched<SMEM, DYN>(sv, S, ray_at(r, t_min));
         if (COUNT) cn->sdf_evals += n0.evals;
         if (n0.ref == omd::REF_NONE) return out;  // `marched.is_none()` -> INF -> return rec (also every NaN ray)
         float aux = n0.d;
         int steps = 0;
         while (aux < HIT_SIZE && steps < UNSTUCK_MAX_STEPS) {
             new_t += MIN_STEP_SIZE;
-            aux = abs_sdf_of(sv, S, n0.ref, ray_at(r, new_t));
+            aux = abs_sdf_of<SMEM, DYN>(sv, S, n0.ref, ray_at(r, new_t));
             steps++;
             if (COUNT) cn->sdf_evals++;
         }
@@ -636,7 +705,7 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
     while (t < t_max && t < closest && max_march_iter > 0) {
         max_march_iter--;
         const V3 point = ray_at(r, t);
-        const Near n = ACCEL ? nearest_marched_accel(sv, S, point, stk) : nearest_marched(sv, S, point);
+        const Near n = ACCEL ? nearest_marched_accel(sv, S, point, stk) : nearest_marched<SMEM, DYN>(sv, S, point);
         if (COUNT) { cn->march_steps++; cn->sdf_evals += n.evals; }
         if (n.ref == omd::REF_NONE) return out;  // `material.is_none()`
         if (n.d < HIT_SIZE) {
@@ -645,7 +714,7 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
             out.t = t;
             out.ref = n.ref;
             out.point = point;
-            out.normal = marched_normal(sv, S, n.ref, point);
+            out.normal = marched_normal<SMEM, DYN>(sv, S, n.ref, point);
             if (COUNT) cn->normal_evals++;
             return out;
         }
@@ -656,7 +725,8 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
 
 // FrozenHittableList::hit (hits.rs:270-334); also first_hit (the BVH subsumes CameraHash).
 // Warp-collective: all 32 lanes call it, `alive` marks the lanes that carry a ray.
-// MA: 0 = the scene has no candidate grid / distance BVH, 1 = it has, 2 = look at the header (parity hooks)
+// MA: 0 = the scene has no candidate grid / distance BVH and no dyn marched objects, 1 = it has the structures,
+// 3 = it has dyn marched objects (om_dyn_marched), 2 = look at the header (parity hooks)
 template <bool SMEM, bool COUNT, int MA>
 __device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, bool alive,
                                                 Counters& cn, int2* stack) {
@@ -675,10 +745,12 @@ __device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const
         const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, t_min, fminf(t_max, h.t));
         if (te < kInf) {
             auto run = [&]() -> Hit {
-                if constexpr (MA == 0) return march<SMEM, COUNT, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
-                else if constexpr (MA == 1) return march<SMEM, COUNT, true>(sv, S, r, t_min, t_max, h.t, &cn, stack);
-                else return (S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u ? march<SMEM, COUNT, true>(sv, S, r, t_min, t_max, h.t, &cn, stack)
-                                                                   : march<SMEM, COUNT, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+                if constexpr (MA == 0) return march<SMEM, COUNT, false, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+                else if constexpr (MA == 1) return march<SMEM, COUNT, true, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+                else if constexpr (MA == 3) return march<SMEM, COUNT, false, true>(sv, S, r, t_min, t_max, h.t, &cn, stack);
+                else return S.n[omd::PT_MDYN] != 0u ? march<SMEM, COUNT, false, true>(sv, S, r, t_min, t_max, h.t, &cn, stack)
+                            : ((S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u ? march<SMEM, COUNT, true, false>(sv, S, r, t_min, t_max, h.t, &cn, stack)
+                                                                       : march<SMEM, COUNT, false, false>(sv, S, r, t_min, t_max, h.t, &cn, stack));
             };
             const Hit m = run();
             if (m.ref != omd::REF_NONE) h = m;
@@ -703,7 +775,7 @@ __device__ __forceinline__ Material load_material(const SceneView<SMEM>& sv, con
     m.bloom_lo = __float_as_uint(m1.z); m.bloom_hi = __float_as_uint(m1.w);
     return m;
 }
-template <bool SMEM>
+template <bool SMEM, bool DYN = true>
 __device__ __forceinline__ void finish_hit(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, Hit& h) {
     const uint32_t type = omd::ref_type(h.ref), i = omd::ref_index(h.ref);
     if (type == omd::PT_SPHERE) {  // traced.rs:57-61
@@ -744,7 +816,7 @@ __device__ __forceinline__ void finish_hit(const SceneView<SMEM>& sv, const Scen
         h.normal = n * copysignf(1.f, -div);
     } else {  // marched hit (hits.rs:322-328): the accepted point and the nearest object's normal there
         h.point = ray_at(r, h.t);
-        h.normal = marched_normal(sv, S, h.ref, h.point);
+        h.normal = marched_normal<SMEM, DYN>(sv, S, h.ref, h.point);
     }
 }
 
@@ -989,7 +1061,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
                 bool finished;
                 V3 result = color;
                 if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
-                    finish_hit(sv, S, ray, A.tmin, h);
+                    finish_hit<SMEM, MA == 3>(sv, S, ray, A.tmin, h);
                     const Material m = load_material(sv, S, h.ref);
                     if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
                     color = color * scatter(m, ray, h.point, h.normal, g);

@@ -369,4 +369,33 @@ bool generate(SceneLists& s, uint32_t kind, uint64_t seed, uint64_t n_param) {
     }
 }
 
+// om_scene_add_dyn_marched: the program must keep the operand stack within [0, OM_SDF_STACK], end with one value,
+// name existing registers and read them only after a write.  The device interpreter (om_device.cuh, sdf_program) and
+// the oracle's rely on this check instead of guarding every step.
+const char* check_sdf_program(const uint32_t* code, size_t n_words) {
+    if (n_words == 0 || n_words > OM_SDF_MAX_WORDS) return "program must have 1..OM_SDF_MAX_WORDS words";
+    int depth = 0;
+    bool written[OM_SDF_REGS] = {false, false, false, false};
+    for (size_t pc = 0; pc < n_words; pc++) {
+        const uint32_t op = code[pc] & 0xFFu, arg = code[pc] >> 8;
+        int need = 0, delta = 0;
+        switch (op) {
+            case OM_SDF_X: case OM_SDF_Y: case OM_SDF_Z: delta = 1; break;
+            case OM_SDF_CONST: delta = 1; if (++pc >= n_words) return "OM_SDF_CONST without its value word"; break;
+            case OM_SDF_ADD: case OM_SDF_SUB: case OM_SDF_MUL: case OM_SDF_DIV: case OM_SDF_MIN: case OM_SDF_MAX: case OM_SDF_LEN2: need = 2; delta = -1; break;
+            case OM_SDF_LEN3: need = 3; delta = -2; break;
+            case OM_SDF_NEG: case OM_SDF_ABS: case OM_SDF_SQRT: need = 1; break;
+            case OM_SDF_STORE: need = 1; delta = -1; if (arg >= OM_SDF_REGS) return "register out of range"; written[arg] = true; break;
+            case OM_SDF_LOAD: delta = 1; if (arg >= OM_SDF_REGS) return "register out of range"; if (!written[arg]) return "register read before it is written"; break;
+            default: return "unknown opcode";
+        }
+        if (op != OM_SDF_STORE && op != OM_SDF_LOAD && op != OM_SDF_CONST && arg != 0u) return "argument bits set on an opcode that takes none";
+        if (op == OM_SDF_CONST && arg != 0u) return "argument bits set on an opcode that takes none";
+        if (depth < need) return "operand stack underflow";
+        depth += delta;
+        if (depth > OM_SDF_STACK) return "operand stack overflow";
+    }
+    return depth == 1 ? "" : "program must leave exactly one value on the stack";
+}
+
 }  // namespace omh

@@ -1,3 +1,4 @@
+#include <type_traits>
 // Host-side launch wrappers, compiled once per build of om_device.cuh (namespace OM_NS).
 namespace OM_NS {
 
@@ -6,24 +7,29 @@ static cudaError_t prep(K kern, size_t smem_bytes) {
     return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
 }
 
-// k_render<SMEM, COUNT, MA>: MA = 1 when the scene carries a candidate grid / distance BVH over its marched objects
+// k_render<SMEM, COUNT, MA>: MA = 1 when the scene carries a candidate grid / distance BVH over its marched objects,
+// MA = 3 when it has dyn marched objects (om_dyn_marched), else 0
 template <class F>
-static void with_render_kernel(bool smem, bool count, bool maccel, F f) {
-    if (smem) {
-        if (count) { if (maccel) f(k_render<true, true, 1>); else f(k_render<true, true, 0>); }
-        else { if (maccel) f(k_render<true, false, 1>); else f(k_render<true, false, 0>); }
-    } else {
-        if (count) { if (maccel) f(k_render<false, true, 1>); else f(k_render<false, true, 0>); }
-        else { if (maccel) f(k_render<false, false, 1>); else f(k_render<false, false, 0>); }
-    }
+static void with_render_kernel(bool smem, bool count, int ma, F f) {
+    auto pick = [&](auto SM, auto CN) {
+        constexpr bool sm = decltype(SM)::value, cn = decltype(CN)::value;
+        if (ma == 1) f(k_render<sm, cn, 1>);
+        else if (ma == 3) f(k_render<sm, cn, 3>);
+        else f(k_render<sm, cn, 0>);
+    };
+    if (smem) { if (count) pick(std::true_type{}, std::true_type{}); else pick(std::true_type{}, std::false_type{}); }
+    else { if (count) pick(std::false_type{}, std::true_type{}); else pick(std::false_type{}, std::false_type{}); }
 }
-static bool scene_has_march_accel(const omk::RenderArgs& a) { return (a.scene.mgrid_dim[0] | a.scene.n_mbvh_nodes) != 0u; }
+static int scene_march_variant(const omk::RenderArgs& a) {
+    if (a.scene.n[omd::PT_MDYN] != 0u) return 3;
+    return (a.scene.mgrid_dim[0] | a.scene.n_mbvh_nodes) != 0u ? 1 : 0;
+}
 
 // resident CTAs per SM of the render kernel for this configuration (the same for both MA instances: one launch bound)
 int render_occupancy(bool smem, bool count, size_t smem_bytes) {
     int n = 0;
     cudaError_t e = cudaSuccess;
-    with_render_kernel(smem, count, false, [&](auto kern) {
+    with_render_kernel(smem, count, 0, [&](auto kern) {
         if (smem) prep(kern, smem_bytes);
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, RENDER_THREADS, smem ? smem_bytes : 0);
     });
@@ -31,7 +37,7 @@ int render_occupancy(bool smem, bool count, size_t smem_bytes) {
 }
 
 cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st) {
-    with_render_kernel(smem, count, scene_has_march_accel(a), [&](auto kern) {
+    with_render_kernel(smem, count, scene_march_variant(a), [&](auto kern) {
         if (smem) prep(kern, smem_bytes);
         kern<<<grid, RENDER_THREADS, smem ? smem_bytes : 0, st>>>(a);
     });

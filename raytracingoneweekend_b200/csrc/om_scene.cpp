@@ -357,8 +357,9 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     h.n[PT_PARA] = uint32_t(L.parallelograms.size());
     h.n[PT_MSPHERE] = uint32_t(L.marched_spheres.size()); h.n[PT_MBOX] = uint32_t(L.marched_boxes.size());
     h.n[PT_MTORUS] = uint32_t(L.marched_tori.size());
+    h.n[PT_MDYN] = uint32_t(L.dyn_marched.size());
     out.n_total = 0;
-    for (int i = 0; i < 8; i++) out.n_total += h.n[i];
+    for (uint32_t i = 0; i < PT_COUNT; i++) out.n_total += h.n[i];
 
     // ---- bounded traced primitives -> BVH; unbounded / scene-sized ones -> always-test list ----
     // `reach`: how far a ray origin can be from an object it still has to find.  Origins are the
@@ -521,16 +522,40 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
         }
         grow(lo, hi);
     }
+    // Arc<dyn Marched> as data: transforms + where the object's local_sdf program sits in the code pool
+    h.off_hot[PT_MDYN] = hot.units();
+    for (size_t i = 0; i < L.dyn_marched.size(); i++) {
+        const om_dyn_marched& s = L.dyn_marched[i];
+        hot.rows3(s.m_world_to_local);
+        hot.rows3(s.m_local_to_world);
+        hot.f4(s.world_f, u2f(L.dyn_code_first[i]), u2f(L.dyn_code_first[i + 1] - L.dyn_code_first[i]), 0.f);
+        double lo[3], hi[3];
+        for (int a = 0; a < 3; a++) {  // the user's box (or +-INF = draw always), padded like the others
+            const double pad = 4 * HIT + 1e-3 * std::max(std::fabs(double(s.bounds_lo[a])), std::fabs(double(s.bounds_hi[a])));
+            lo[a] = std::isfinite(s.bounds_lo[a]) ? s.bounds_lo[a] - pad : -1e300;
+            hi[a] = std::isfinite(s.bounds_hi[a]) ? s.bounds_hi[a] + pad : 1e300;
+        }
+        grow(lo, hi);
+    }
+    h.off_dyn_code = hot.units();
+    for (size_t i = 0; i < L.dyn_code.size(); i += 4) {
+        uint32_t w[4] = {0, 0, 0, 0};
+        for (size_t k = 0; k < 4 && i + k < L.dyn_code.size(); k++) w[k] = L.dyn_code[i + k];
+        hot.u4(w[0], w[1], w[2], w[3]);
+    }
     h.off_sph_mat = hot.units();
     for (size_t i = 0; i < L.spheres.size(); i += 16) {
         uint32_t w[4] = {0, 0, 0, 0};
         for (size_t k = 0; k < 16 && i + k < L.spheres.size(); k++) w[k >> 2] |= (L.spheres[i + k].material.mat_type & 0xFFu) << (8 * (k & 3));
         hot.u4(w[0], w[1], w[2], w[3]);
     }
-    h.n_marched = h.n[PT_MSPHERE] + h.n[PT_MBOX] + h.n[PT_MTORUS];
+    h.n_marched = h.n[PT_MSPHERE] + h.n[PT_MBOX] + h.n[PT_MTORUS] + h.n[PT_MDYN];
     for (int a = 0; a < 3; a++) {
         if (h.n_marched == 0) { h.march_lo[a] = kInf; h.march_hi[a] = -kInf; }
-        else { h.march_lo[a] = nextafterf(float(mlo[a]), -kInf); h.march_hi[a] = nextafterf(float(mhi[a]), kInf); }
+        else {  // (a dyn marched object without bounds makes the union infinite: every ray marches)
+            h.march_lo[a] = mlo[a] < -3e38 ? -kInf : nextafterf(float(mlo[a]), -kInf);
+            h.march_hi[a] = mhi[a] > 3e38 ? kInf : nextafterf(float(mhi[a]), kInf);
+        }
     }
     h.hot_units = hot.units();
 
@@ -550,9 +575,14 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     };
     mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
     mats(PT_PARA, L.parallelograms); mats(PT_MSPHERE, L.marched_spheres); mats(PT_MBOX, L.marched_boxes); mats(PT_MTORUS, L.marched_tori);
+    mats(PT_MDYN, L.dyn_marched);
     lap("pack hot + cold images");
-    build_marched_grid(L, h, cold);
-    if (!(flags & 8u)) build_marched_bvh(L, h, cold);
+    // The candidate grid and the distance BVH need analytic bounds of every |sdf|; a user program has none, so a scene
+    // with dyn marched objects is marched by the plain scan (hits.rs:301-320).
+    if (L.dyn_marched.empty()) {
+        build_marched_grid(L, h, cold);
+        if (!(flags & 8u)) build_marched_bvh(L, h, cold);
+    }
     if (cold.units() == 0) cold.f4(0, 0, 0, 0);
     if (hot.units() == 0) hot.f4(0, 0, 0, 0);
     h.hot_units = hot.units();

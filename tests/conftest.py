@@ -43,6 +43,8 @@ def oracle_scene_from(O, frozen):
     o = O.OracleScene()
     for k, arr in frozen.lists().items():
         o.add(k, arr)
+    for pod, code in frozen.dyn_marched():
+        o.add_dyn_marched(pod, code)
     return o
 
 
