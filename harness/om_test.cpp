@@ -46,7 +46,19 @@ static void host_checks() {
     w += MarchedTorus::new_(Mat4x4::translate(0, 3, 0), Vec3::new_(0.5f, 0.1f, 0.f), die);
     CHECK(w.len() == 8 && w.spheres.size() == 1 && w.cubes.size() == 1 && w.triangles.size() == 1 && w.parallelograms.size() == 1 && w.infinite_planes.size() == 1 &&
           w.marched_spheres.size() == 1 && w.marched_boxes.size() == 1 && w.marched_tori.size() == 1);
-    // user trait objects cannot cross to a device (hits.rs:91-100)
+    // a user's Marched type as data (hits.rs:96-100): local_sdf = |p| - 1 as a program; malformed programs are refused
+    const SdfProgram unit_ball = SdfProgram().x().y().z().len3().c(1.f).sub();
+    w += DynMarched::new_(Mat4x4::translate(0, 0, -10), Mat4x4::translate(0, 0, 10), 1.f, unit_ball, lam);
+    CHECK(w.len() == 9 && w.marched_objects.size() == 1 && w.marched_objects[0].local_sdf.words.size() == 7);
+    {
+        HittableList bad;
+        bad += DynMarched::new_(Mat4x4::identity(), Mat4x4::identity(), 1.f, SdfProgram().x().add(), lam);  // stack underflow
+        CHECK(status_of([&] { bad.freeze(&c); }) == OM_ERR_INVALID);
+        bad.clear();
+        bad += DynMarched::new_(Mat4x4::identity(), Mat4x4::identity(), 1.f, SdfProgram().load(2), lam);  // register never written
+        CHECK(status_of([&] { bad.freeze(&c); }) == OM_ERR_INVALID);
+    }
+    // native trait objects cannot cross to a device (hits.rs:91-95)
     int dummy = 0;
     CHECK(status_of([&] { w += static_cast<const void*>(&dummy); }) == OM_ERR_UNSUPPORTED);
     // freeze needs no device; the frozen scene knows what it holds
@@ -54,6 +66,9 @@ static void host_checks() {
     uint64_t n[8];
     check(om_scene_counts(fz.handle(), n));
     CHECK(n[0] == 1 && n[3] == 1 && n[7] == 1);
+    uint64_t n_dyn = 0;
+    check(om_scene_dyn_marched_count(fz.handle(), &n_dyn));
+    CHECK(n_dyn == 1);
     w.clear();
     CHECK(w.len() == 0);
     // the generated random_scene arrives through the same lists (ground + small spheres + 3 big ones; torus, parallelogram, triangle, cube)
@@ -86,6 +101,17 @@ static void gpu_checks() {
     CHECK(rec.t == 2.f && rec.normal.y() == 1.f && rec.obj_id == OM_OBJ_ID(OM_TYPE_INFINITE_PLANE, 0));
     // a ray parallel to the plane misses it (|n.d| < 1e-6, traced.rs:93)
     CHECK(!fz.hit(Ray::new_(Point3::new_(5, 0, 0), Vec3::new_(1, 0, 0)), 0.001f, 100.f, &rec));
+
+    // a dyn marched unit ball at (0,0,10) (marched.rs:14-44 defaults over a program): from (0,0,5) along +z the march lands on
+    // the near pole, numeric normal with the sign fix points back at the ray
+    {
+        HittableList wd;
+        wd += DynMarched::new_(Mat4x4::translate(0, 0, -10), Mat4x4::translate(0, 0, 10), 1.f, SdfProgram().x().y().z().len3().c(1.f).sub(), lam);
+        const FrozenHittableList fd = wd.freeze(nullptr);
+        CHECK(fd.hit(Ray::new_(Point3::new_(0, 0, 5), Vec3::new_(0, 0, 1)), 0.001f, 100.f, &rec));
+        CHECK(near(rec.t, 4.f) && near(rec.point.z(), 9.f) && rec.normal.z() == -1.f && rec.obj_id == OM_OBJ_ID(OM_TYPE_DYN_MARCHED, 0));
+        CHECK(!fd.hit(Ray::new_(Point3::new_(0, 3, 5), Vec3::new_(0, 0, 1)), 0.001f, 100.f, &rec));
+    }
 
     // render: the union of N threads' chunks equals one thread's image, bit for bit, and the counter ends at width*height*spp
     const Camera cam = Camera::new_(Point3::new_(13, 2, 3), Point3::new_(0, 0, 0), Vec3::new_(0, 1, 0), 20.f, 1.5f, 0.1f, 10.f);

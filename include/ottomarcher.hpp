@@ -18,6 +18,8 @@
 #define OTTOMARCHER_HPP
 
 #include <algorithm>
+#include <cmath>
+#include <cstring>
 #include <atomic>
 #include <cstdint>
 #include <stdexcept>
@@ -111,6 +113,50 @@ struct MarchedTorus : om_marched_torus {
     static MarchedTorus new_(const Mat4x4& local_to_world, Vec3 sizes, const Material& mat) { MarchedTorus t; om_marched_torus_new(&t, local_to_world.m, sizes.e, &mat); return t; }  // marched.rs:115
 };
 
+// A user's `impl Marched` (marched.rs:8-45) as data, for `world += Arc::new(obj) as Arc<dyn Marched + Send + Sync>`
+// (hits.rs:96-100): to_local / to_world as matrices, to_world_f as a factor, local_sdf as a postfix f32 program
+// (OM_SDF_* in ottomarcher.h).  sdf() and get_outward_normal() are the trait's defaults.
+struct SdfProgram {
+    std::vector<uint32_t> words;
+    SdfProgram& op(uint32_t opcode, uint32_t arg = 0) { words.push_back(OM_SDF_INSN(opcode, arg)); return *this; }
+    SdfProgram& x() { return op(OM_SDF_X); }
+    SdfProgram& y() { return op(OM_SDF_Y); }
+    SdfProgram& z() { return op(OM_SDF_Z); }
+    SdfProgram& c(float v) { uint32_t b; std::memcpy(&b, &v, 4); words.push_back(OM_SDF_CONST); words.push_back(b); return *this; }
+    SdfProgram& add() { return op(OM_SDF_ADD); }
+    SdfProgram& sub() { return op(OM_SDF_SUB); }
+    SdfProgram& mul() { return op(OM_SDF_MUL); }
+    SdfProgram& div() { return op(OM_SDF_DIV); }
+    SdfProgram& min() { return op(OM_SDF_MIN); }
+    SdfProgram& max() { return op(OM_SDF_MAX); }
+    SdfProgram& neg() { return op(OM_SDF_NEG); }
+    SdfProgram& abs() { return op(OM_SDF_ABS); }
+    SdfProgram& sqrt() { return op(OM_SDF_SQRT); }
+    SdfProgram& len2() { return op(OM_SDF_LEN2); }
+    SdfProgram& len3() { return op(OM_SDF_LEN3); }
+    SdfProgram& store(uint32_t r) { return op(OM_SDF_STORE, r); }
+    SdfProgram& load(uint32_t r) { return op(OM_SDF_LOAD, r); }
+};
+struct DynMarched {
+    om_dyn_marched pod;
+    SdfProgram local_sdf;
+    // `bounds` = Bounded::build_world_bounding_box (bounding_box.rs:69-73); nullptr = the trait default (draw always)
+    static DynMarched new_(const Mat4x4& world_to_local, const Mat4x4& local_to_world, float world_f, const SdfProgram& prog, const Material& mat,
+                           const Point3* bounds_lo = nullptr, const Point3* bounds_hi = nullptr) {
+        DynMarched d;
+        std::memcpy(d.pod.m_world_to_local, world_to_local.m, sizeof d.pod.m_world_to_local);
+        std::memcpy(d.pod.m_local_to_world, local_to_world.m, sizeof d.pod.m_local_to_world);
+        d.pod.world_f = world_f;
+        for (int i = 0; i < 3; i++) {
+            d.pod.bounds_lo[i] = bounds_lo ? bounds_lo->e[i] : -INFINITY;
+            d.pod.bounds_hi[i] = bounds_hi ? bounds_hi->e[i] : INFINITY;
+        }
+        d.pod.material = mat;
+        d.local_sdf = prog;
+        return d;
+    }
+};
+
 // ---- camera.rs:38-59 ----------------------------------------------------------------------------------
 struct Camera : om_camera {
     static Camera new_(Point3 lookfrom, Point3 lookat, Vec3 vup, float vfov_in_degrees, float aspect_ratio, float aperture, float focus_dist) {
@@ -146,11 +192,12 @@ public:
     std::vector<om_marched_sphere> marched_spheres;
     std::vector<om_marched_box> marched_boxes;
     std::vector<om_marched_torus> marched_tori;
+    std::vector<DynMarched> marched_objects;  // Vec<Arc<dyn Marched + Send + Sync>> (hits.rs:40), as data
 
     static HittableList new_() { return HittableList(); }  // hits.rs:72
     void clear() {                                          // hits.rs:81
         spheres.clear(); cubes.clear(); triangles.clear(); infinite_planes.clear(); parallelograms.clear();
-        marched_spheres.clear(); marched_boxes.clear(); marched_tori.clear();
+        marched_spheres.clear(); marched_boxes.clear(); marched_tori.clear(); marched_objects.clear();
     }
     // impl AddAssign<&T> for HittableList (hits.rs:101-110)
     HittableList& operator+=(const Sphere& o) { spheres.push_back(o); return *this; }
@@ -161,7 +208,9 @@ public:
     HittableList& operator+=(const MarchedSphere& o) { marched_spheres.push_back(o); return *this; }
     HittableList& operator+=(const MarchedBox& o) { marched_boxes.push_back(o); return *this; }
     HittableList& operator+=(const MarchedTorus& o) { marched_tori.push_back(o); return *this; }
-    // AddAssign<Arc<dyn Traced>> / <Arc<dyn Marched>> (hits.rs:91-100): a user trait object cannot cross to the device
+    // AddAssign<Arc<dyn Marched + Send + Sync>> (hits.rs:96-100) for a Marched type described as data
+    HittableList& operator+=(const DynMarched& o) { marched_objects.push_back(o); return *this; }
+    // AddAssign<Arc<dyn Traced>> (hits.rs:91-95) and native trait objects: compiled host code cannot cross to the device
     HittableList& operator+=(const void* dyn_object) {
         om_scene* s = nullptr;
         check(om_scene_create(&s));
@@ -172,7 +221,7 @@ public:
     }
     size_t len() const {
         return spheres.size() + cubes.size() + triangles.size() + infinite_planes.size() + parallelograms.size() + marched_spheres.size() +
-               marched_boxes.size() + marched_tori.size();
+               marched_boxes.size() + marched_tori.size() + marched_objects.size();
     }
     // The library's seeded synthetic scenes (om_scene_generate), pulled back into host lists so that they enter the
     // renderer the same way a hand-built world does.
@@ -212,6 +261,7 @@ public:
             check(om_scene_add_marched_spheres(h_, hl.marched_spheres.data(), hl.marched_spheres.size()));
             check(om_scene_add_marched_boxes(h_, hl.marched_boxes.data(), hl.marched_boxes.size()));
             check(om_scene_add_marched_tori(h_, hl.marched_tori.data(), hl.marched_tori.size()));
+            for (const DynMarched& d : hl.marched_objects) check(om_scene_add_dyn_marched(h_, &d.pod, d.local_sdf.words.data(), d.local_sdf.words.size()));
             check(om_scene_freeze(h_, cam, flags));
         } catch (...) { om_scene_destroy(h_); h_ = nullptr; throw; }
     }

@@ -53,6 +53,23 @@ pub struct om_marched_torus {
     pub m_local_to_world_translate_rotate: [f32; 16], pub m_world_to_local_translate_rotate: [f32; 16],
     pub m_local_to_world_scale: [f32; 4], pub m_world_to_local_scale: [f32; 4], pub sizes: [f32; 3], pub material: om_material,
 }
+/// `Arc<dyn Marched + Send + Sync>` as data (marched.rs:8-45): to_local / to_world matrices, to_world_f factor, world bounds
+/// (or +-INF); local_sdf travels beside it as a postfix f32 program (OM_SDF_* opcodes, see ottomarcher.h).
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct om_dyn_marched {
+    pub m_world_to_local: [f32; 16], pub m_local_to_world: [f32; 16], pub world_f: f32,
+    pub bounds_lo: [f32; 3], pub bounds_hi: [f32; 3], pub material: om_material,
+}
+pub const OM_SDF_X: u32 = 1; pub const OM_SDF_Y: u32 = 2; pub const OM_SDF_Z: u32 = 3; pub const OM_SDF_CONST: u32 = 4;
+pub const OM_SDF_ADD: u32 = 5; pub const OM_SDF_SUB: u32 = 6; pub const OM_SDF_MUL: u32 = 7; pub const OM_SDF_DIV: u32 = 8;
+pub const OM_SDF_MIN: u32 = 9; pub const OM_SDF_MAX: u32 = 10; pub const OM_SDF_NEG: u32 = 11; pub const OM_SDF_ABS: u32 = 12;
+pub const OM_SDF_SQRT: u32 = 13; pub const OM_SDF_LEN2: u32 = 14; pub const OM_SDF_LEN3: u32 = 15;
+pub const OM_SDF_STORE: u32 = 16; pub const OM_SDF_LOAD: u32 = 17;
+pub const fn om_sdf_insn(op: u32, arg: u32) -> u32 { op | (arg << 8) }
+/// A user type opts in by describing itself as data; `impl DeviceMarched for MyShape` next to `impl Marched for MyShape`.
+pub trait DeviceMarched {
+    fn describe(&self) -> (om_dyn_marched, Vec<u32>);
+}
 /// camera.rs:9-29
 #[repr(C)] #[derive(Clone, Copy)]
 pub struct om_camera {
@@ -83,6 +100,9 @@ extern "C" {
     pub fn om_scene_add_marched_spheres(s: *mut om_scene, a: *const om_marched_sphere, n: usize) -> om_status;
     pub fn om_scene_add_marched_boxes(s: *mut om_scene, a: *const om_marched_box, n: usize) -> om_status;
     pub fn om_scene_add_marched_tori(s: *mut om_scene, a: *const om_marched_torus, n: usize) -> om_status;
+    pub fn om_scene_add_dyn_marched(s: *mut om_scene, obj: *const om_dyn_marched, code: *const u32, n_words: usize) -> om_status;
+    pub fn om_scene_dyn_marched_count(s: *const om_scene, count: *mut u64) -> om_status;
+    pub fn om_scene_get_dyn_marched(s: *const om_scene, index: u64, obj: *mut om_dyn_marched, code: *mut u32, n_words: *mut usize) -> om_status;
     pub fn om_scene_add_dyn_object(s: *mut om_scene, trait_object: *const c_void) -> om_status;
     pub fn om_scene_freeze(s: *mut om_scene, cam: *const om_camera, flags: u32) -> om_status;
     pub fn om_render_create(out: *mut *mut om_render, frozen: *const om_scene, cam: *const om_camera, p: *const om_render_params) -> om_status;
@@ -118,6 +138,8 @@ pub struct SceneLists {
     pub spheres: Vec<om_sphere>, pub cubes: Vec<om_cube>, pub triangles: Vec<om_barycentric>,
     pub infinite_planes: Vec<om_infinite_plane>, pub parallelograms: Vec<om_barycentric>,
     pub marched_spheres: Vec<om_marched_sphere>, pub marched_boxes: Vec<om_marched_box>, pub marched_tori: Vec<om_marched_torus>,
+    /// marched_objects: Vec<Arc<dyn Marched + Send + Sync>> (hits.rs:40) whose types implement DeviceMarched
+    pub marched_objects: Vec<(om_dyn_marched, Vec<u32>)>,
 }
 
 /// Replaces main.rs:196-214 (spawn of the render threads): renders `spp` samples per pixel
@@ -137,6 +159,7 @@ pub fn render_gpu(cam: &om_camera, world: &SceneLists, max_depth: u32, tmin: f32
             ck(om_scene_add_marched_spheres(s, world.marched_spheres.as_ptr(), world.marched_spheres.len()))?;
             ck(om_scene_add_marched_boxes(s, world.marched_boxes.as_ptr(), world.marched_boxes.len()))?;
             ck(om_scene_add_marched_tori(s, world.marched_tori.as_ptr(), world.marched_tori.len()))?;
+            for (obj, code) in &world.marched_objects { ck(om_scene_add_dyn_marched(s, obj, code.as_ptr(), code.len()))?; }
             ck(om_scene_freeze(s, cam, 0))?;
             let p = om_render_params { width, height, spp_max: spp, max_depth, tmin, tmax, seed, flags, device: -1, ..Default::default() };
             let mut r: *mut om_render = std::ptr::null_mut();
