@@ -438,6 +438,10 @@ OM_API om_status om_scene_generate(om_scene* s, uint32_t kind, uint64_t seed, ui
 OM_API const char* om_last_error(void); /* thread-local, never NULL */
 OM_API const char* om_version(void);
 OM_API int32_t om_device_count(void);
+/* The library keeps the large device blocks of destroyed render handles (framebuffer, read-out staging, wavefront
+ * pools; at most 4 GiB per process) for the next om_render_create of the same size: cudaMalloc/cudaFree of a frame
+ * cost up to a fifth of a render.  This releases them to the driver.                                          */
+OM_API om_status om_trim_device_cache(void);
 /* FP32 FMA microbenchmark on `device`: achieved TFLOP/s (2 flop per FMA lane) and SM clock.    */
 OM_API om_status om_bench_fp32_peak(int32_t device, float* tflops, float* ms);
 

@@ -23,6 +23,7 @@ PROTOTYPES = {
     "om_scene_create": ("st", [P(vp)]),
     "om_scene_clear": ("st", [vp]),
     "om_scene_destroy": ("st", [vp]),
+    "om_trim_device_cache": ("st", []),
     "om_scene_add_spheres": ("st", [vp, P(A.Sphere), sz]),
     "om_scene_add_cubes": ("st", [vp, P(A.Cube), sz]),
     "om_scene_add_triangles": ("st", [vp, P(A.Barycentric), sz]),

@@ -286,10 +286,10 @@ struct om_render {
 namespace {
 om_status ensure_staging(om_render* r, size_t bytes) {
     if (r->staging_bytes >= bytes) return OM_OK;
-    if (r->staging) cudaFree(r->staging);
+    if (r->staging) dev_free(r->staging);
     r->staging = nullptr;
     r->staging_bytes = 0;
-    CU(cudaMalloc(&r->staging, bytes));
+    CU(dev_alloc(&r->staging, bytes));
     r->staging_bytes = bytes;
     return OM_OK;
 }
@@ -352,10 +352,10 @@ om_status om_render_destroy(om_render* r) {
     if (r->stream) cudaStreamSynchronize(r->stream);
     for (EventPair& e : r->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (EventPair& e : r->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    cudaFree(r->acc); cudaFree(r->aux); cudaFree(r->jitter); cudaFree(r->counters); cudaFree(r->live_list); cudaFree(r->live_count); cudaFree(r->owners); cudaFree(r->chunk_counts); cudaFree(r->staging);
+    dev_free(r->acc); dev_free(r->aux); cudaFree(r->jitter); cudaFree(r->counters); dev_free(r->live_list); cudaFree(r->live_count); cudaFree(r->owners); cudaFree(r->chunk_counts); dev_free(r->staging);
     if (r->wf.n_slots) {
-        cudaFree(r->wf.s_ray); cudaFree(r->wf.s_st); cudaFree(r->wf.s_live);
-        cudaFree(r->wf.q_ray[0]); cudaFree(r->wf.q_ray[1]); cudaFree(r->wf.q_march[0]); cudaFree(r->wf.q_march[1]); cudaFree(r->wf.q_shade[0]); cudaFree(r->wf.q_shade[1]); cudaFree(r->wf.ctr);
+        dev_free(r->wf.s_ray); dev_free(r->wf.s_st); dev_free(r->wf.s_live);
+        dev_free(r->wf.q_ray[0]); dev_free(r->wf.q_ray[1]); dev_free(r->wf.q_march[0]); dev_free(r->wf.q_march[1]); dev_free(r->wf.q_shade[0]); dev_free(r->wf.q_shade[1]); cudaFree(r->wf.ctr);
     }
     if (r->wf_host_ctr) cudaFreeHost(r->wf_host_ctr);
     for (int i = 0; i < 2; i++) if (r->wf_ev[i]) cudaEventDestroy(r->wf_ev[i]);
@@ -403,8 +403,8 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
         if (s2 != OM_OK) return s2;
         CU(cudaStreamCreateWithFlags(&r->own_stream, cudaStreamNonBlocking));
         r->stream = r->own_stream;
-        CU(cudaMalloc(&r->acc, size_t(r->npx) * sizeof(float4)));
-        CU(cudaMalloc(&r->aux, size_t(r->npx) * sizeof(uint4)));
+        CU(dev_alloc(&r->acc, size_t(r->npx) * sizeof(float4)));
+        CU(dev_alloc(&r->aux, size_t(r->npx) * sizeof(uint4)));
         CU(cudaMalloc(&r->jitter, p.spp_max));
         CU(cudaMalloc(&r->counters, omk::ctr::CTR_COUNT * sizeof(unsigned long long)));
         CU(cudaMemsetAsync(r->acc, 0, size_t(r->npx) * sizeof(float4), r->stream));
@@ -415,7 +415,7 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
         CU(cudaMemcpyAsync(r->jitter, jt.data(), p.spp_max, cudaMemcpyHostToDevice, r->stream));
         CU(cudaStreamSynchronize(r->stream));
         if (p.flags & OM_RENDER_ADAPTIVE) {
-            CU(cudaMalloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t)));
+            CU(dev_alloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t)));
             CU(cudaMalloc(&r->live_count, sizeof(uint32_t)));
         }
         // launch shape: persistent grid of one CTA per SM, hot image in shared memory when it fits
@@ -450,9 +450,9 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             if (const char* e = getenv("OM_WF_SLOTS")) { const long v = atol(e); if (v >= 1024 && v <= (1l << 24)) want = (uint32_t)v; }  // tuning knob
             const uint32_t n_slots = std::min<uint32_t>(want, (r->npx + 31u) & ~31u);
             omk::WfArgs& w = r->wf;
-            CU(cudaMalloc(&w.s_ray, size_t(n_slots) * 32)); CU(cudaMalloc(&w.s_st, size_t(n_slots) * 64)); CU(cudaMalloc(&w.s_live, (size_t(n_slots) + 511u) & ~size_t(511)));
-            CU(cudaMalloc(&w.q_ray[0], size_t(n_slots) * 4)); CU(cudaMalloc(&w.q_ray[1], size_t(n_slots) * 4)); CU(cudaMalloc(&w.q_march[0], size_t(n_slots) * 4)); CU(cudaMalloc(&w.q_march[1], size_t(n_slots) * 4));
-            for (int i = 0; i < 2; i++) CU(cudaMalloc(&w.q_shade[i], size_t(n_slots) * 4 * omk::wf::N_CLS));
+            CU(dev_alloc(&w.s_ray, size_t(n_slots) * 32)); CU(dev_alloc(&w.s_st, size_t(n_slots) * 64)); CU(dev_alloc(&w.s_live, (size_t(n_slots) + 511u) & ~size_t(511)));
+            CU(dev_alloc(&w.q_ray[0], size_t(n_slots) * 4)); CU(dev_alloc(&w.q_ray[1], size_t(n_slots) * 4)); CU(dev_alloc(&w.q_march[0], size_t(n_slots) * 4)); CU(dev_alloc(&w.q_march[1], size_t(n_slots) * 4));
+            for (int i = 0; i < 2; i++) CU(dev_alloc(&w.q_shade[i], size_t(n_slots) * 4 * omk::wf::N_CLS));
             CU(cudaMalloc(&w.ctr, omk::wf::G_WORDS * 4));
             w.n_slots = n_slots;
             CU(cudaMallocHost(&r->wf_host_ctr, 2 * omk::wf::G_WORDS * 4));
@@ -582,7 +582,7 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     a.spp_pass = spp_this_pass ? spp_this_pass : r->budget;
     const bool adaptive = (r->p.flags & OM_RENDER_ADAPTIVE) != 0;
     if (r->owners) {  // scheduled ownership: the pixels to walk are decided now, from the state and the table of this moment
-        if (!r->live_list) { CU(cudaMalloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t))); CU(cudaMalloc(&r->live_count, sizeof(uint32_t))); }
+        if (!r->live_list) { CU(dev_alloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t))); CU(cudaMalloc(&r->live_count, sizeof(uint32_t))); }
         CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
         k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, adaptive ? 1u : 0u, 0u, 1u, r->owners, r->owner_id, r->live_list, r->live_count);
         CU(cudaGetLastError());

@@ -104,6 +104,7 @@ extern "C" {
     pub fn om_scene_dyn_marched_count(s: *const om_scene, count: *mut u64) -> om_status;
     pub fn om_scene_get_dyn_marched(s: *const om_scene, index: u64, obj: *mut om_dyn_marched, code: *mut u32, n_words: *mut usize) -> om_status;
     pub fn om_scene_add_dyn_object(s: *mut om_scene, trait_object: *const c_void) -> om_status;
+    pub fn om_trim_device_cache() -> om_status;
     pub fn om_scene_freeze(s: *mut om_scene, cam: *const om_camera, flags: u32) -> om_status;
     pub fn om_render_create(out: *mut *mut om_render, frozen: *const om_scene, cam: *const om_camera, p: *const om_render_params) -> om_status;
     pub fn om_render_destroy(r: *mut om_render) -> om_status;
