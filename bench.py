@@ -39,6 +39,9 @@ NCU_DRAM_BYTES = {("C2", 1024, 1, False): 121891584 + 557661952}  # profiles/r1_
 FLOPS = dict(raygen=73, accumulate=20, node_visit=48, prim_test=61, sdf_eval=56, normal_eval=210, shade=50)
 
 
+_OUT = sys.stdout
+
+
 def flops_per_sample(c, samples):
     """Algorithmic flops of one sample from executed-work counters (OM_RENDER_COUNTERS run)."""
     s = float(samples)
@@ -153,7 +156,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.perf_counter() - t_all,
     }
-    print(json.dumps(line), flush=True)
+    _OUT.write(json.dumps(line) + "\n"); _OUT.flush()
 
 
 def run_ours(args):
@@ -308,7 +311,7 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if line:
-        print(json.dumps(line), flush=True)
+        _OUT.write(json.dumps(line) + "\n"); _OUT.flush()
 
 
 def main():
@@ -322,6 +325,12 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--wavefront", action="store_true", help="use the wavefront pipeline (OM_RENDER_WAVEFRONT) instead of the persistent kernel")
     args = ap.parse_args()
+    # ONE JSON line on stdout: native libraries print there too (NCCL's version banner under NCCL_DEBUG), so file
+    # descriptor 1 is pointed at stderr for the run and the line goes to a private copy of the real stdout.
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
