@@ -306,6 +306,7 @@ omk::RenderArgs make_args(const om_render* r) {
     a.max_depth = r->p.max_depth;
     a.tmin = r->p.tmin; a.tmax = r->p.tmax;
     a.seed_lo = uint32_t(r->p.seed); a.seed_hi = uint32_t(r->p.seed >> 32);
+    for (uint32_t k = 0; k < 10; k++) { a.rk[2 * k] = a.seed_lo + k * 0x9E3779B9u; a.rk[2 * k + 1] = a.seed_hi + k * 0xBB67AE85u; }
     a.flags = r->p.flags;
     a.part_rank = r->p.part_rank; a.part_world = r->p.part_world ? r->p.part_world : 1u;
     if (a.part_world > 1u) {

@@ -29,6 +29,7 @@ struct RenderArgs {
     uint32_t max_depth;
     float tmin, tmax;
     uint32_t seed_lo, seed_hi;
+    uint32_t rk[20];       // Philox round keys: rk[2r] = seed_lo + r * 0x9E3779B9, rk[2r+1] = seed_hi + r * 0xBB67AE85 (r = 0..9)
     uint32_t flags;        // OM_RENDER_*
     uint32_t part_rank, part_world;
     uint32_t n_work;       // work slots (pixels padded to whole 8x4 tiles / chunks)

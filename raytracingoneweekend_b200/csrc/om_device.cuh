@@ -47,7 +47,8 @@ using namespace omk::ctr;
 // rand::thread_rng (utils.rs:24-27).  Same contract as omh::Rng / the oracle's ref::Rng.
 // ============================================================================================
 struct Rng {
-    uint32_t k0, k1, a, b, draw;
+    const uint32_t* rk;  // the launch's round keys (RenderArgs::rk, kernel parameter space: they fold into the XORs as constant-bank operands)
+    uint32_t a, b, draw;
     uint32_t b0, b1, b2, b3;
 };
 // Inlined at a handful of draw sites that the warp reaches CONVERGED (see rng_take): the first
@@ -61,19 +62,18 @@ __device__ __forceinline__
 #else
 __device__ __noinline__
 #endif
-uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
+uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, const uint32_t* rk) {
     uint32_t c3 = 0u;  // STREAM_PATH
 #pragma unroll
     for (int r = 0; r < 10; r++) {
         const uint32_t lo0 = 0xD2511F53u * c0, hi0 = __umulhi(0xD2511F53u, c0);
         const uint32_t lo1 = 0xCD9E8D57u * c2, hi1 = __umulhi(0xCD9E8D57u, c2);
-        c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        c0 = hi1 ^ c1 ^ rk[2 * r]; c1 = lo1; c2 = hi0 ^ c3 ^ rk[2 * r + 1]; c3 = lo0;  // key schedule precomputed by the host
     }
     return make_uint4(c0, c1, c2, c3);
 }
-__device__ __forceinline__ void rng_init(Rng& g, uint32_t k0, uint32_t k1, uint32_t pixel, uint32_t sample) {
-    g.k0 = k0; g.k1 = k1; g.a = pixel; g.b = sample; g.draw = 0;
+__device__ __forceinline__ void rng_init(Rng& g, const uint32_t* rk, uint32_t pixel, uint32_t sample) {
+    g.rk = rk; g.a = pixel; g.b = sample; g.draw = 0;
 }
 __device__ __forceinline__ float u32_to_f32(uint32_t u) { return (float)(u >> 8) * 5.9604644775390625e-8f; }  // utils.rs:25: uniform [0,1), 24 bits
 __device__ __forceinline__ uint32_t sel4(uint32_t i, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -88,7 +88,7 @@ __device__ __forceinline__ void rng_take(Rng& g, float* out) {
     const uint32_t pos = g.draw & 3u;
     const bool need = pos == 0u || pos + (uint32_t)N > 4u;
     uint4 nb = make_uint4(g.b0, g.b1, g.b2, g.b3);
-    if (need) nb = philox4x32_10((g.draw + (uint32_t)N - 1u) >> 2, g.a, g.b, g.k0, g.k1);
+    if (need) nb = philox4x32_10((g.draw + (uint32_t)N - 1u) >> 2, g.a, g.b, g.rk);
 #pragma unroll
     for (int i = 0; i < N; i++) {
         const uint32_t j = pos + (uint32_t)i;
@@ -1035,7 +1035,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
 
         // ---- per-lane path state machine; the loop itself is warp-uniform ----
         Rng g;
-        rng_init(g, A.seed_lo, A.seed_hi, 0u, 0u);
+        rng_init(g, A.rk, 0u, 0u);
         g.b0 = g.b1 = g.b2 = g.b3 = 0u;
         Ray ray;
         ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
@@ -1049,7 +1049,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
             if (align) phase_bar_count(1);
             if (alive && fresh) {
                 const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
-                rng_init(g, A.seed_lo, A.seed_hi, pxl, sample);
+                rng_init(g, A.rk, pxl, sample);
                 ray = primary_ray(A, pxl, sample, g);
                 color = v3(1.f, 1.f, 1.f);
                 seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
@@ -1135,7 +1135,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_primary(const __grid_constan
         ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
         if (alive) {
             if (mode == 0u) ray = center_ray(A, pxl);
-            else { Rng g; rng_init(g, A.seed_lo, A.seed_hi, pxl, sample_index); ray = primary_ray(A, pxl, sample_index, g); }
+            else { Rng g; rng_init(g, A.rk, pxl, sample_index); ray = primary_ray(A, pxl, sample_index, g); }
         }
         const Hit h = closest_hit_warp<SMEM, false, 2>(sv, A.scene, ray, A.tmin, A.tmax, (A.flags & OM_RENDER_BRUTE_FORCE) != 0, alive, cn, stack);
         if (alive) {

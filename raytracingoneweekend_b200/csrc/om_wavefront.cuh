@@ -364,7 +364,7 @@ __global__ void __launch_bounds__(WF_THREADS, 4) k_wf_shade(const __grid_constan
         float first_t = kInf;
         uint32_t seg = 0, first_lo = 0, first_hi = 0;
         Rng g;
-        rng_init(g, A.seed_lo, A.seed_hi, 0u, 0u);
+        rng_init(g, A.rk, 0u, 0u);
         g.b0 = g.b1 = g.b2 = g.b3 = 0u;
         if (have && W.init) { slot = i; need_pixel = true; }
         if (have && !W.init) {
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(WF_THREADS, 4) k_wf_shade(const __grid_constan
             sample = __float_as_uint(o.w); pix = __float_as_uint(d.w);
             color = v3(th.x, th.y, th.z); first_t = th.w;
             seg = __float_as_uint(mi.x); first_lo = __float_as_uint(mi.z); first_hi = __float_as_uint(mi.w);
-            rng_init(g, A.seed_lo, A.seed_hi, pix, sample);
+            rng_init(g, A.rk, pix, sample);
             g.draw = __float_as_uint(mi.y);
             const uint32_t href = __float_as_uint(hm.y);
             bool finished;
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(WF_THREADS, 4) k_wf_shade(const __grid_constan
                 const Material m = load_material(sv, S, h.ref);
                 if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
                 if ((g.draw & 3u) != 0u) {  // the block the stream is in the middle of (not carried between kernels)
-                    const uint4 b = philox4x32_10(g.draw >> 2, g.a, g.b, g.k0, g.k1);
+                    const uint4 b = philox4x32_10(g.draw >> 2, g.a, g.b, g.rk);
                     g.b0 = b.x; g.b1 = b.y; g.b2 = b.z; g.b3 = b.w;
                 }
                 color = color * scatter(m, ray, h.point, h.normal, g);
@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(WF_THREADS, 4) k_wf_shade(const __grid_constan
             if (pn < target && !(adaptive && A.aux[p].y >= 5u)) { pix = p; sample = A.sample_base + pn; fresh = true; need_pixel = false; }
         }
         if (fresh) {  // render_thread.rs:183-192: jittered (u,v), camera ray
-            rng_init(g, A.seed_lo, A.seed_hi, pix, sample);
+            rng_init(g, A.rk, pix, sample);
             ray = primary_ray(A, pix, sample, g);
             color = v3(1.f, 1.f, 1.f);
             seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
