@@ -89,12 +89,16 @@ __device__ __forceinline__ void rng_take(Rng& g, float* out) {
     const bool need = pos == 0u || pos + (uint32_t)N > 4u;
     uint4 nb = make_uint4(g.b0, g.b1, g.b2, g.b3);
     if (need) nb = philox4x32_10((g.draw + (uint32_t)N - 1u) >> 2, g.a, g.b, g.rk);
+    // words pos .. pos+N-1 of the window {cached block (the new one when pos == 0), new block}: a two-level barrel shift
+    // by pos (the first version picked every word through two 4-way select chains: 57 instructions for N = 3)
+    static_assert(N >= 1 && N <= 3, "the window below holds words 0..6");
+    const bool z = pos == 0u, s2 = (pos & 2u) != 0u, s1 = (pos & 1u) != 0u;
+    uint32_t x[7] = {z ? nb.x : g.b0, z ? nb.y : g.b1, z ? nb.z : g.b2, z ? nb.w : g.b3, nb.x, nb.y, nb.z};
+    uint32_t y[N + 1];
 #pragma unroll
-    for (int i = 0; i < N; i++) {
-        const uint32_t j = pos + (uint32_t)i;
-        const uint32_t w = (pos != 0u && j < 4u) ? sel4(j, g.b0, g.b1, g.b2, g.b3) : sel4(j & 3u, nb.x, nb.y, nb.z, nb.w);
-        out[i] = u32_to_f32(w);
-    }
+    for (int i = 0; i <= N; i++) y[i] = s2 ? x[i + 2] : x[i];
+#pragma unroll
+    for (int i = 0; i < N; i++) out[i] = u32_to_f32(s1 ? y[i + 1] : y[i]);
     g.b0 = nb.x; g.b1 = nb.y; g.b2 = nb.z; g.b3 = nb.w;
     g.draw += (uint32_t)N;
 }
