@@ -316,7 +316,8 @@ omk::RenderArgs make_args(const om_render* r) {
         a.tiles_x = 0;
     } else {
         a.tiles_x = (r->p.width + 7u) / 8u;
-        a.n_work = a.tiles_x * ((r->p.height + 3u) / 4u) * 32u;
+        // tiles are handed out in blocks of 2 x 4 (16 x 16 pixels, see work_to_pixel): whole blocks, the surplus maps to no pixel
+        a.n_work = ((a.tiles_x + 1u) / 2u) * ((((r->p.height + 3u) / 4u) + 3u) / 4u) * 8u * 32u;
     }
     a.jitter = r->jitter;
     a.acc = r->acc; a.aux = r->aux;

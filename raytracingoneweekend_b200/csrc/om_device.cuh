@@ -656,6 +656,12 @@ __device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& 
 // cache) meet at a named barrier at the top of the path loop and again between the closest-hit query and shading, so that
 // they stream the same part of this 70 KB kernel at the same time.  The count variant also tells the warps that ran out of
 // tickets when the last warp of their group has left the loop.
+#ifndef OM_GROUP_TICKETS
+#define OM_GROUP_TICKETS 8
+#endif
+#ifndef OM_TILE_BLOCKS
+#define OM_TILE_BLOCKS 1
+#endif
 constexpr int PB_GROUPS = 4;
 constexpr int PB_THREADS = RENDER_THREADS / PB_GROUPS;
 __device__ __forceinline__ unsigned phase_bar_id() { return 1u + ((threadIdx.x >> 5) % (unsigned)PB_GROUPS); }
@@ -955,7 +961,14 @@ __device__ __forceinline__ uint32_t work_to_pixel(const RenderArgs& A, uint32_t 
         return p < A.npx ? p : 0xFFFFFFFFu;
     }
     const uint32_t tile = k >> 5, in = k & 31u;
+#if OM_TILE_BLOCKS
+    // 8 consecutive tickets = a block of 2 x 4 tiles = 16 x 16 pixels (the run a phase-aligned warp group draws from)
+    const uint32_t blk = tile >> 3, i = tile & 7u, bx_n = (A.tiles_x + 1u) >> 1;
+    const uint32_t tx = (blk % bx_n) * 2u + (i & 1u), ty = (blk / bx_n) * 4u + (i >> 1);
+    const uint32_t x = tx * 8u + (in & 7u), y = ty * 4u + (in >> 3);
+#else
     const uint32_t x = (tile % A.tiles_x) * 8u + (in & 7u), y = (tile / A.tiles_x) * 4u + (in >> 3);
+#endif
     return (x < A.width && y < A.height) ? y * A.width + x : 0xFFFFFFFFu;
 }
 
@@ -1009,11 +1022,39 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
     const uint32_t lane = threadIdx.x & 31u;
     int2 stack[STACK_DEPTH];
     const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;  // segment 0 + `for _i in 1..depth`
+#if OM_GROUP_TICKETS
+    __shared__ unsigned grp_lock[PB_GROUPS], grp_next[PB_GROUPS], grp_left[PB_GROUPS];
+    if (threadIdx.x < (unsigned)PB_GROUPS) { grp_lock[threadIdx.x] = 0u; grp_next[threadIdx.x] = 0u; grp_left[threadIdx.x] = 0u; }
+    __syncthreads();
+#endif
 
     for (;;) {
         // one ticket = one warp-sized run of 32 work slots (an 8x4 pixel tile)
         uint32_t ticket = 0;
+#if OM_GROUP_TICKETS
+        // the warps of a phase-aligned group draw from a shared run of OM_GROUP_TICKETS consecutive tickets (adjacent tiles:
+        // similar traversal work, less waiting at the group's barriers); single tickets near the end of the launch
+        if (lane == 0u) {
+            if (align) {
+                const uint32_t g = (threadIdx.x >> 5) % (unsigned)PB_GROUPS;
+                while (atomicCAS(&grp_lock[g], 0u, 1u) != 0u) {}
+                __threadfence_block();
+                if (grp_left[g] == 0u) {
+                    const uint32_t n_tickets = (A.n_work + 31u) / 32u;
+                    const uint32_t want = (grp_next[g] + 4u * (uint32_t)OM_GROUP_TICKETS * gridDim.x * (unsigned)PB_GROUPS < n_tickets) ? (uint32_t)OM_GROUP_TICKETS : 1u;
+                    grp_next[g] = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], (unsigned long long)want);
+                    grp_left[g] = want;
+                }
+                ticket = grp_next[g];
+                grp_next[g] = ticket + 1u;
+                grp_left[g] -= 1u;
+                __threadfence_block();
+                atomicExch(&grp_lock[g], 0u);
+            } else ticket = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], 1ull);
+        }
+#else
         if (lane == 0u) ticket = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], 1ull);
+#endif
         ticket = __shfl_sync(FULL, ticket, 0);
         const uint32_t base = ticket * 32u;
         if (base >= A.n_work) break;
