@@ -34,9 +34,9 @@ WORKLOADS = {
 MAX_DEPTH, TMIN, TMAX = 50, 0.001, 100.0  # main.rs:146,205-206
 # DRAM bytes per k_render launch measured with ncu, keyed by (workload, spp per launch, GPUs, wavefront)
 NCU_DRAM_BYTES = {("C2", 1024, 1, False): 121891584 + 557661952}  # profiles/r1_v1e_c2_1024spp_dram.csv
-# ncu --set full of k_render on C2 (16-spp launch, profiles/r1_v1f_c2_k_render.txt): what the FP32 figure does not show
-NCU_K_RENDER_C2 = {"source": "profiles/r1_v1f_c2_k_render.txt", "issue_active_pct": 60.9, "pipe_fma_cycles_active_pct": 20.8, "inst_executed_pipe_alu_pct": 49.7,
-                   "threads_per_warp_instruction": 13.2, "stall_barrier_per_issue": 4.17, "stall_no_instruction_per_issue": 0.55}
+# ncu --set full of k_render on C2 (16-spp launch, profiles/r1_v1g_c2_k_render.txt): what the FP32 figure does not show
+NCU_K_RENDER_C2 = {"source": "profiles/r1_v1g_c2_k_render.txt", "issue_active_pct": 65.1, "pipe_fma_cycles_active_pct": 22.2, "inst_executed_pipe_alu_pct": 53.1,
+                   "threads_per_warp_instruction": 13.2, "stall_barrier_per_issue": 3.22, "stall_no_instruction_per_issue": 0.40}
 
 # flops "as the reference executes it" per executed unit of work
 FLOPS = dict(raygen=73, accumulate=20, node_visit=48, prim_test=61, sdf_eval=56, normal_eval=210, shade=50)
@@ -286,7 +286,7 @@ def run_ours(args):
         achieved_tf = fps * samples_launch / (launch_ms * 1e-3) / 1e12
         roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf, "traffic": NCU_DRAM_BYTES.get((args.workload, spp, world, wavefront)),
                     "traffic_source": "profiles/r1_v1e_c2_1024spp_dram.csv: ncu dram__bytes_read.sum + dram__bytes_write.sum of this launch (122 MB read + 558 MB written: the 2 x 66 MB "
-                                      "framebuffer pass plus write-backs of the traversal stack); the full section set was captured at 16 spp (profiles/r1_v1f_c2_k_render.txt)" if (args.workload, spp, world, wavefront) in NCU_DRAM_BYTES else None,
+                                      "framebuffer pass plus write-backs of the traversal stack); the full section set was captured at 16 spp (profiles/r1_v1g_c2_k_render.txt)" if (args.workload, spp, world, wavefront) in NCU_DRAM_BYTES else None,
                     "peak_source": "FMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
                     "flops_per_sample": fps, "kernel": "k_wf_extend + k_wf_shade + k_wf_compact (+ k_render tail)" if wavefront else "k_render", "launch_ms": launch_ms,
                     "per_sample": {k: c[k] / c["traced"] for k in ("segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals")},

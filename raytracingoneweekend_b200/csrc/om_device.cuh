@@ -662,7 +662,10 @@ __device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& 
 #ifndef OM_TILE_BLOCKS
 #define OM_TILE_BLOCKS 1
 #endif
-constexpr int PB_GROUPS = 4;
+#ifndef OM_PB_GROUPS
+#define OM_PB_GROUPS 4
+#endif
+constexpr int PB_GROUPS = OM_PB_GROUPS;
 constexpr int PB_THREADS = RENDER_THREADS / PB_GROUPS;
 __device__ __forceinline__ unsigned phase_bar_id() { return 1u + ((threadIdx.x >> 5) % (unsigned)PB_GROUPS); }
 __device__ __forceinline__ int phase_bar_count(int pred) {
