@@ -281,6 +281,10 @@ struct om_render {
     uint32_t* wf_host_ctr = nullptr;  // pinned: wf::G_WORDS words per in-flight batch (2 batches)
     cudaEvent_t wf_ev[2] = {nullptr, nullptr};
     uint32_t n_uniform = 0;       // samples every live pixel has after the launches so far
+    // tile scheduling: see refresh_block_order
+    uint32_t* block_order = nullptr;
+    uint32_t* tile_cost = nullptr;
+    bool have_order = false;
 };
 
 namespace {
@@ -308,6 +312,8 @@ omk::RenderArgs make_args(const om_render* r) {
     a.seed_lo = uint32_t(r->p.seed); a.seed_hi = uint32_t(r->p.seed >> 32);
     for (uint32_t k = 0; k < 10; k++) { a.rk[2 * k] = a.seed_lo + k * 0x9E3779B9u; a.rk[2 * k + 1] = a.seed_hi + k * 0xBB67AE85u; }
     a.flags = r->p.flags;
+    a.block_order = r->have_order ? r->block_order : nullptr;
+    a.tile_cost = nullptr;
     a.part_rank = r->p.part_rank; a.part_world = r->p.part_world ? r->p.part_world : 1u;
     if (a.part_world > 1u) {
         const uint32_t chunks = (r->npx + OM_CHUNK_PIXELS - 1) / OM_CHUNK_PIXELS;
@@ -354,7 +360,7 @@ om_status om_render_destroy(om_render* r) {
     if (r->stream) cudaStreamSynchronize(r->stream);
     for (EventPair& e : r->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (EventPair& e : r->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    dev_free(r->acc); dev_free(r->aux); cudaFree(r->jitter); cudaFree(r->counters); dev_free(r->live_list); cudaFree(r->live_count); cudaFree(r->owners); cudaFree(r->chunk_counts); dev_free(r->staging);
+    cudaFree(r->block_order); cudaFree(r->tile_cost); dev_free(r->acc); dev_free(r->aux); cudaFree(r->jitter); cudaFree(r->counters); dev_free(r->live_list); cudaFree(r->live_count); cudaFree(r->owners); cudaFree(r->chunk_counts); dev_free(r->staging);
     if (r->wf.n_slots) {
         dev_free(r->wf.s_ray); dev_free(r->wf.s_st); dev_free(r->wf.s_live);
         dev_free(r->wf.q_ray[0]); dev_free(r->wf.q_ray[1]); dev_free(r->wf.q_march[0]); dev_free(r->wf.q_march[1]); dev_free(r->wf.q_shade[0]); dev_free(r->wf.q_shade[1]); cudaFree(r->wf.ctr);
@@ -577,10 +583,65 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
 }
 }  // namespace
 
+namespace {
+// Tile scheduling.  A warp owns a tile for all of its samples and tile costs are heavy-tailed (C2: the tiles on the marched torus
+// take several times the average), so the launch ends when the last expensive tile does: measured with time stamps, the average
+// warp was out of tickets at 144 ms of a 154 ms launch in row order and at 147 of 184 ms when the expensive band came last.  A
+// fixed-spp launch of 32 samples or more on the persistent kernel therefore starts with a PILOT launch of 1/64 of the samples in
+// which k_render files every tile's cost; the blocks are then handed out most expensive first for the rest of this launch and for
+// later launches of the handle.  Same pixels in any order (the passes of a handle are bit-identical to one launch).
+bool can_order_blocks(const om_render* r) {
+    if (r->p.flags & (OM_RENDER_WAVEFRONT | OM_RENDER_ADAPTIVE)) return false;
+    if (r->p.part_world > 1u || r->owners || getenv("OM_NO_BLOCK_ORDER")) return false;
+    const uint32_t tiles_x = (r->p.width + 7u) / 8u, tiles_y = (r->p.height + 3u) / 4u;
+    return ((tiles_x + 1u) / 2u) * ((tiles_y + 3u) / 4u) >= 8u * (uint32_t)r->props.sms;
+}
+om_status refresh_block_order(om_render* r) {
+    const uint32_t tiles_x = (r->p.width + 7u) / 8u, tiles_y = (r->p.height + 3u) / 4u, nb = ((tiles_x + 1u) / 2u) * ((tiles_y + 3u) / 4u);
+    std::vector<uint32_t> cost(size_t(nb) * 8u);
+    CU(cudaMemcpyAsync(cost.data(), r->tile_cost, cost.size() * 4u, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    std::vector<uint64_t> key(nb);
+    for (uint32_t b = 0; b < nb; b++) {
+        uint64_t c = 0;
+        for (uint32_t i = 0; i < 8u; i++) c = std::max<uint64_t>(c, cost[size_t(b) * 8u + i]);  // a block is a run of 8 tiles for 8 warps: its longest tile
+        key[b] = c;
+    }
+    std::vector<uint32_t> order(nb);
+    for (uint32_t b = 0; b < nb; b++) order[b] = b;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return key[x] > key[y]; });
+    if (!r->block_order) CU(cudaMalloc(&r->block_order, size_t(nb) * 4u));
+    CU(cudaMemcpyAsync(r->block_order, order.data(), size_t(nb) * 4u, cudaMemcpyHostToDevice, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    r->have_order = true;
+    return OM_OK;
+}
+om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot);
+}  // namespace
+
 om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     if (!r) return fail(OM_ERR_INVALID, "om_render_launch: NULL handle");
     CU(cudaSetDevice(r->dev));
+    const uint32_t want = spp_this_pass ? spp_this_pass : r->budget;
+    const uint32_t todo = (uint32_t)std::min<uint64_t>(r->budget, uint64_t(r->n_uniform) + want) - r->n_uniform;
+    if (!r->have_order && todo >= 32u && can_order_blocks(r)) {
+        const uint32_t pilot = std::max(1u, todo / 64u);
+        const uint32_t tiles_x = (r->p.width + 7u) / 8u, tiles_y = (r->p.height + 3u) / 4u, nb = ((tiles_x + 1u) / 2u) * ((tiles_y + 3u) / 4u);
+        if (!r->tile_cost) CU(cudaMalloc(&r->tile_cost, size_t(nb) * 8u * 4u));
+        CU(cudaMemsetAsync(r->tile_cost, 0, size_t(nb) * 8u * 4u, r->stream));
+        om_status s = launch_pass(r, pilot, true);
+        if (s != OM_OK) return s;
+        s = refresh_block_order(r);
+        if (s != OM_OK) return s;
+        return launch_pass(r, todo - pilot, false);
+    }
+    return launch_pass(r, spp_this_pass, false);
+}
+
+namespace {
+om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
     omk::RenderArgs a = make_args(r);
+    if (pilot) a.tile_cost = r->tile_cost;
     a.spp_pass = spp_this_pass ? spp_this_pass : r->budget;
     const bool adaptive = (r->p.flags & OM_RENDER_ADAPTIVE) != 0;
     if (r->owners) {  // scheduled ownership: the pixels to walk are decided now, from the state and the table of this moment
@@ -621,6 +682,7 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
     r->launches++;
     return OM_OK;
 }
+}  // namespace
 
 om_status om_render_sync(om_render* r) {
     if (!r) return fail(OM_ERR_INVALID, "om_render_sync: NULL handle");

@@ -40,6 +40,10 @@ struct RenderArgs {
     unsigned long long* counters;
     const uint32_t* live_list;  // adaptive mode: compacted list of live pixels, or nullptr
     const uint32_t* live_count;
+    // Tile scheduling (om_api_render.inl, refresh_block_order): the order in which the 16 x 16-pixel blocks are handed out
+    // (most expensive first) or nullptr = row order; and where k_render leaves each tile's cost (cycles / 16) for the next order
+    const uint32_t* block_order;
+    uint32_t* tile_cost;
 };
 
 // Wavefront pipeline (om_wavefront.cuh).  A SLOT carries one path; it is bound to one pixel until

@@ -966,7 +966,9 @@ __device__ __forceinline__ uint32_t work_to_pixel(const RenderArgs& A, uint32_t 
     const uint32_t tile = k >> 5, in = k & 31u;
 #if OM_TILE_BLOCKS
     // 8 consecutive tickets = a block of 2 x 4 tiles = 16 x 16 pixels (the run a phase-aligned warp group draws from)
-    const uint32_t blk = tile >> 3, i = tile & 7u, bx_n = (A.tiles_x + 1u) >> 1;
+    uint32_t blk = tile >> 3;
+    if (A.block_order) blk = __ldg(A.block_order + blk);
+    const uint32_t i = tile & 7u, bx_n = (A.tiles_x + 1u) >> 1;
     const uint32_t tx = (blk % bx_n) * 2u + (i & 1u), ty = (blk / bx_n) * 4u + (i >> 1);
     const uint32_t x = tx * 8u + (in & 7u), y = ty * 4u + (in >> 3);
 #else
@@ -1061,6 +1063,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         ticket = __shfl_sync(FULL, ticket, 0);
         const uint32_t base = ticket * 32u;
         if (base >= A.n_work) break;
+        const uint32_t tile_t0 = (uint32_t)clock64();
         const uint32_t k = base + lane;
         const uint32_t pxl = k < A.n_work ? work_to_pixel(A, k) : 0xFFFFFFFFu;
         const bool valid = pxl != 0xFFFFFFFFu;
@@ -1138,6 +1141,12 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         if (touched) {
             A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
             A.aux[pxl] = make_uint4(__float_as_uint(st.avg_depth), st.bad_avgs, st.bloom_lo, st.bloom_hi);
+        }
+        // what this tile cost, filed under its place in the image (the host orders the next launch's blocks by it)
+        if (A.tile_cost && lane == 0u) {
+            uint32_t blk = ticket >> 3;
+            if (A.block_order) blk = __ldg(A.block_order + blk);
+            A.tile_cost[blk * 8u + (ticket & 7u)] = ((uint32_t)clock64() - tile_t0) >> 4;  // 32-bit cycle counter: tiles are far shorter than its 2 s period
         }
     }
 
