@@ -316,7 +316,12 @@ OM_API om_status om_render_destroy(om_render* r); /* NULL is fine */
  * stream) instead of the handle's own; NULL switches back.  The caller keeps ownership.        */
 OM_API om_status om_render_set_stream(om_render* r, void* cuda_stream);
 /* Trace up to `spp_this_pass` more samples of every live pixel (sample-major passes, the
- * reference's outer loop render_thread.rs:176).  Asynchronous.  0 = all remaining samples.    */
+ * reference's outer loop render_thread.rs:176).  Asynchronous.  0 = all remaining samples.
+ * Tile scheduling: the first fixed-spp launch of 32 samples or more on the persistent kernel is split
+ * into a pilot launch of 1/64 of the samples, which measures what every 8x4 tile costs, and the
+ * rest, whose 16x16-pixel blocks are then handed out most expensive first (a warp owns a tile for all
+ * of its samples, so the launch ends when the last expensive tile does).  That call blocks for the
+ * duration of the pilot; the order is kept for later launches of the handle.  Same pixels either way. */
 OM_API om_status om_render_launch(om_render* r, uint32_t spp_this_pass);
 OM_API om_status om_render_sync(om_render* r);
 /* the AtomicU64 progress counter (main.rs:148, render_thread.rs:196-198): +1 per sample, plus
