@@ -377,6 +377,39 @@ def test_phase_alignment_changes_nothing(api, A, kind, seed, adaptive):
         assert out[0][1:] == o[1:]
 
 
+@pytest.mark.parametrize("kind,seed", [("random_scene", 1), ("rtiow_classic", 1)])
+def test_cost_ordered_tile_scheduling_changes_nothing(api, A, kind, seed, monkeypatch):
+    """A fixed-spp launch of 32 samples or more is split into a pilot launch (1/64 of the samples, files every tile's cost)
+    and the rest with the 16x16-pixel blocks handed out most expensive first (om_render_launch / refresh_block_order).  Same
+    pixels and counters as the plain row order (OM_NO_BLOCK_ORDER), as a later launch of the same handle, and as passes."""
+    fz = api.FrozenHittableList.generate(kind, seed)
+    cam = cam_rtiow(api, 4 / 3)
+    W, H, spp = 800, 600, 40  # 50 x 38 blocks >= 8 per SM
+    out = []
+    for mode in ("ordered", "rows", "passes"):
+        if mode == "rows":
+            monkeypatch.setenv("OM_NO_BLOCK_ORDER", "1")
+        else:
+            monkeypatch.delenv("OM_NO_BLOCK_ORDER", raising=False)
+        r = api.Renderer(fz, cam, api.render_params(W, H, spp, seed=4, flags=A.RENDER_PERSISTENT))
+        if mode == "passes":
+            r.launch(33); r.launch(0)  # pilot inside the first launch, the order reused by the second
+        else:
+            r.launch(0)
+        r.sync()
+        px, kernels = r.read_pixels(), r.perf_counters()["kernels"]
+        assert r.samples_traced() == W * H * spp and r.samples_done() == W * H * spp
+        assert kernels == {"ordered": 2, "rows": 1, "passes": 3}[mode]
+        if mode == "ordered":  # the same handle again, now without a pilot
+            r.reset(); r.launch(0); r.sync()
+            assert_pixels_equal(r.read_pixels(), px)
+            assert r.perf_counters()["kernels"] == 3
+        r.close()
+        out.append(px)
+    assert_pixels_equal(out[0], out[1])
+    assert_pixels_equal(out[0], out[2])
+
+
 def test_pipeline_flags_exclusive(api, A, rtiow):
     fz, _ = rtiow
     with pytest.raises(Exception):
