@@ -334,7 +334,9 @@ OM_API om_status om_render_samples_traced(om_render* r, uint64_t* traced);
  * [9] segments that entered the march loop.  [3..9] need OM_RENDER_COUNTERS.
  * Host side: [10] kernels launched by om_render_launch since create, [11] the flags in force
  * (with OM_RENDER_WAVEFRONT or OM_RENDER_PERSISTENT as chosen when the caller set neither),
- * [12] 1 if that pipeline keeps the scene image in shared memory.  Synchronises.              */
+ * [12] 1 if that pipeline keeps the scene image in shared memory.  Device again (OM_RENDER_COUNTERS,
+ * persistent kernel): [13] path-loop iterations summed over warps, [14] the same summed over the lanes
+ * that carried a path ([14] / (32 * [13]) = lane occupancy of the loop).  Synchronises.        */
 OM_API om_status om_render_perf_counters(om_render* r, uint64_t out[16]);
 /* device time of the launches since the last call to this function, in ms (CUDA events on the
  * render stream).  Synchronises.                                                              */

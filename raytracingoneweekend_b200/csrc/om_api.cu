@@ -309,7 +309,8 @@ om_status om_scene_stats(const om_scene* s, uint64_t st[8]) {
     if (!s || !st || !s->frozen) return fail(OM_ERR_INVALID, "om_scene_stats: scene not frozen");
     st[0] = s->fz.hdr.n_nodes; st[1] = s->fz.hdr.bvh_depth; st[2] = s->fz.hdr.n_bvh_prims; st[3] = s->fz.hdr.n_large;
     st[4] = uint64_t(s->fz.hdr.hot_units) * 16u + uint64_t(s->fz.hdr.cold_units) * 16u;
-    st[5] = ((uint64_t(s->fz.hdr.hot_units) * 16u <= 224u * 1024u) ? 1 : 0) | (s->fz.hdr.dyn_pad != 0.f ? 2 : 0);
+    // bit 0: the scene image and k_render's traversal stacks fit the 227 KB of shared memory of one CTA
+    st[5] = ((uint64_t(s->fz.hdr.hot_units) * 16u + om_exact::render_stack_bytes(s->fz.hdr.stack_need) + 2048u <= 227u * 1024u && s->fz.hdr.n_nodes <= 16384u) ? 1 : 0) | (s->fz.hdr.dyn_pad != 0.f ? 2 : 0);
     st[6] = uint64_t(s->fz.hdr.mgrid_dim[0]) * s->fz.hdr.mgrid_dim[1] * s->fz.hdr.mgrid_dim[2];
     st[7] = st[6] ? uint64_t(s->fz.hdr.cold_units - s->fz.hdr.off_mgrid_lists) * 4u : 0u;
     return OM_OK;

@@ -272,7 +272,8 @@ struct om_render {
     uint64_t kernels = 0;         // kernels launched by om_render_launch since create (om_render_perf_counters [10])
     bool use_smem = false;       // k_render: scene image in shared memory (one 1024-thread CTA per SM)
     bool use_smem_hook = false;  // parity-hook kernels (two 256-thread CTAs per SM)
-    size_t smem_bytes = 0;
+    size_t smem_bytes = 0;       // k_render: scene image + traversal stacks
+    size_t smem_hook_bytes = 0;  // parity hooks: the same for their 256-thread CTAs
     int grid = 0;
     // wavefront pipeline (OM_RENDER_WAVEFRONT)
     omk::WfArgs wf;               // device arrays; n_slots == 0: not allocated
@@ -431,9 +432,13 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
         const size_t hot_bytes = size_t(r->scene->fz.hdr.hot_units) * 16u;
         // (per-ray box padding lives in the global-memory variants only, see node_slab)
         const bool may_stage = !(p.flags & OM_RENDER_NO_SMEM_SCENE) && r->scene->fz.hdr.dyn_pad == 0.f;
-        r->use_smem = may_stage && hot_bytes + 2048u <= r->props.smem_optin;
-        r->use_smem_hook = may_stage && hot_bytes + 1024u <= r->props.smem_optin / 2;
-        r->smem_bytes = hot_bytes;  // each launch wrapper uses it only when its kernel keeps the scene in shared memory
+        // a staged scene brings the traversal stacks into shared memory with it (TravStack<true, ..>: 4-byte entries, 14-bit node index)
+        const uint32_t stack_need = r->scene->fz.hdr.stack_need;
+        const bool small_tree = r->scene->fz.hdr.n_nodes <= 16384u;
+        r->smem_bytes = hot_bytes + om_exact::render_stack_bytes(stack_need);  // each launch wrapper uses these only when its kernel keeps the scene in shared memory
+        r->smem_hook_bytes = hot_bytes + om_exact::hook_stack_bytes(stack_need);
+        r->use_smem = may_stage && small_tree && r->smem_bytes + 2048u <= r->props.smem_optin;
+        r->use_smem_hook = may_stage && small_tree && r->smem_hook_bytes + 1024u <= r->props.smem_optin / 2;
         int occ = exact ? om_exact::render_occupancy(r->use_smem, count, r->smem_bytes) : om_fast::render_occupancy(r->use_smem, count, r->smem_bytes);
         if (occ < 1) {
             cudaError_t e = cudaGetLastError();
@@ -509,7 +514,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     const bool exact = (r->p.flags & OM_RENDER_FAST_MATH) == 0, count = (r->p.flags & OM_RENDER_COUNTERS) != 0;
     omk::WfArgs w = r->wf;
     w.n_target = n_target;
-    const size_t smem = r->wf_smem ? r->smem_bytes : 0;
+    const size_t smem = r->wf_smem ? size_t(r->scene->fz.hdr.hot_units) * 16u : 0;  // the extend kernel stages the scene image only (its stacks are in local memory)
     CU(cudaMemsetAsync(w.ctr, 0, omk::wf::G_WORDS * 4, r->stream));
     CU(cudaMemsetAsync(w.s_live, 0, (size_t(w.n_slots) + 511u) & ~size_t(511), r->stream));
     w.it = 0; w.init = 1;
@@ -803,8 +808,8 @@ om_status om_render_primary(om_render* r, uint32_t mode, uint32_t sample_index, 
     float* d_t = (float*)(d_ids + n);
     omk::RenderArgs a = make_args(r);
     const int grid = std::min(ublocks(n), r->props.sms * 8);
-    cudaError_t e = !(r->p.flags & OM_RENDER_FAST_MATH) ? om_exact::launch_primary(a, r->use_smem_hook, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t)
-                                                   : om_fast::launch_primary(a, r->use_smem_hook, grid, r->smem_bytes, r->stream, mode, sample_index, d_ids, d_t);
+    cudaError_t e = !(r->p.flags & OM_RENDER_FAST_MATH) ? om_exact::launch_primary(a, r->use_smem_hook, grid, r->smem_hook_bytes, r->stream, mode, sample_index, d_ids, d_t)
+                                                   : om_fast::launch_primary(a, r->use_smem_hook, grid, r->smem_hook_bytes, r->stream, mode, sample_index, d_ids, d_t);
     if (e != cudaSuccess) return fail(OM_ERR_CUDA, "k_primary launch failed: %s", cudaGetErrorString(e));
     CU(cudaMemcpyAsync(ids, d_ids, n * 8u, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaMemcpyAsync(t, d_t, n * 4u, cudaMemcpyDeviceToHost, r->stream));
@@ -922,9 +927,10 @@ om_status om_trace_rays(const om_scene* frozen, const float* origins, const floa
     if (e == cudaSuccess) e = cudaMemcpy(d_d, dirs, b_rays, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "om_trace_rays: upload failed: %s", cudaGetErrorString(e)));
     const size_t hot_bytes = size_t(frozen->fz.hdr.hot_units) * 16u;
-    const bool smem = !(flags & OM_RENDER_NO_SMEM_SCENE) && frozen->fz.hdr.dyn_pad == 0.f && hot_bytes + 1024u <= props.smem_optin / 2;
+    const size_t smem_bytes = hot_bytes + om_exact::hook_stack_bytes(frozen->fz.hdr.stack_need);  // scene image + traversal stacks
+    const bool smem = !(flags & OM_RENDER_NO_SMEM_SCENE) && frozen->fz.hdr.dyn_pad == 0.f && frozen->fz.hdr.n_nodes <= 16384u && smem_bytes + 1024u <= props.smem_optin / 2;
     const int grid = std::min(ublocks(n), props.sms * 8);
-    e = !(flags & OM_RENDER_FAST_MATH) ? om_exact::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0) : om_fast::launch_trace(a, smem, grid, smem ? hot_bytes : 0, 0);
+    e = !(flags & OM_RENDER_FAST_MATH) ? om_exact::launch_trace(a, smem, grid, smem ? smem_bytes : 0, 0) : om_fast::launch_trace(a, smem, grid, smem ? smem_bytes : 0, 0);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return done(fail(OM_ERR_CUDA, "k_trace_rays failed: %s", cudaGetErrorString(e)));
     if (ids) e = cudaMemcpy(ids, a.ids, b_ids, cudaMemcpyDeviceToHost);

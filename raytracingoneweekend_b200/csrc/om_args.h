@@ -12,7 +12,8 @@ using omd::SceneHeader;
 namespace ctr {
 // slots of RenderArgs::counters; the CTR_SEGMENTS.. ones are only written by the COUNT kernels
 enum { CTR_CREDITED = 0, CTR_TRACED = 1, CTR_TICKET = 2, CTR_SEGMENTS = 3, CTR_NODE_VISITS = 4, CTR_PRIM_TESTS = 5,
-       CTR_SDF_EVALS = 6, CTR_MARCH_STEPS = 7, CTR_NORMAL_EVALS = 8, CTR_MARCH_ENTERED = 9, CTR_COUNT = 16 };
+       CTR_SDF_EVALS = 6, CTR_MARCH_STEPS = 7, CTR_NORMAL_EVALS = 8, CTR_MARCH_ENTERED = 9,
+       CTR_WARP_ITERS = 13 /* path-loop iterations of k_render, per warp */, CTR_LANE_ITERS = 14 /* ... summed over the lanes that carried a path */, CTR_COUNT = 16 };
 
 }  // namespace ctr
 

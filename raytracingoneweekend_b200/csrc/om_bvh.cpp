@@ -242,4 +242,76 @@ void build(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, Bu
     out.depth = depth;
 }
 
+
+namespace {
+struct Kid {
+    int32_t ref;  // binary child reference
+    float lo[3], hi[3];
+};
+float kid_area(const Kid& k) {
+    const float dx = k.hi[0] - k.lo[0], dy = k.hi[1] - k.lo[1], dz = k.hi[2] - k.lo[2];
+    if (!(dx >= 0.f) || !(dy >= 0.f) || !(dz >= 0.f)) return -1.f;
+    return dx * dy + dy * dz + dz * dx;
+}
+void kids_of(const Node& n, Kid& l, Kid& r) {
+    l.ref = n.left; r.ref = n.right;
+    for (int a = 0; a < 3; a++) { l.lo[a] = n.lmin[a]; l.hi[a] = n.lmax[a]; r.lo[a] = n.rmin[a]; r.hi[a] = n.rmax[a]; }
+}
+}  // namespace
+
+void collapse4(const BuildResult& in, Wide4& out, uint32_t width) {
+    out.nodes.clear();
+    out.depth = 0;
+    out.stack_need = 0;
+    if (in.nodes.empty()) return;
+    width = std::min(4u, std::max(2u, width));
+    out.nodes.reserve(in.nodes.size());
+    struct Task { int32_t bin; int32_t wide; uint32_t depth; uint32_t on_stack; };
+    std::vector<Task> todo;
+    out.nodes.push_back(Node4());
+    todo.push_back({0, 0, 1u, 0u});
+    while (!todo.empty()) {
+        const Task t = todo.back();
+        todo.pop_back();
+        out.depth = std::max(out.depth, t.depth);
+        Kid kids[4];
+        uint32_t m = 2;
+        kids_of(in.nodes[size_t(t.bin)], kids[0], kids[1]);
+        if (kids[0].ref == kids[1].ref && kids[0].ref < 0 && kid_area(kids[1]) < 0.f) m = 1;  // the one-primitive root of build()
+        while (m < width) {
+            int best = -1;
+            float best_area = -1.f;
+            for (uint32_t j = 0; j < m; j++) {
+                if (kids[j].ref < 0) continue;
+                const float a = kid_area(kids[j]);
+                if (a > best_area) { best_area = a; best = int(j); }
+            }
+            if (best < 0) break;
+            Kid l, r;
+            kids_of(in.nodes[size_t(kids[best].ref)], l, r);
+            kids[best] = l;
+            kids[m++] = r;
+        }
+        const uint32_t below = t.on_stack + (m - 1u);
+        out.stack_need = std::max(out.stack_need, below);
+        Node4 w;
+        for (uint32_t j = 0; j < 4; j++) {
+            if (j < m) {
+                w.lox[j] = kids[j].lo[0]; w.hix[j] = kids[j].hi[0]; w.loy[j] = kids[j].lo[1]; w.hiy[j] = kids[j].hi[1]; w.loz[j] = kids[j].lo[2]; w.hiz[j] = kids[j].hi[2];
+                if (kids[j].ref < 0) w.child[j] = kids[j].ref;
+                else {
+                    w.child[j] = int32_t(out.nodes.size());
+                    out.nodes.push_back(Node4());
+                    todo.push_back({kids[j].ref, w.child[j], t.depth + 1u, below});
+                }
+            } else {
+                w.lox[j] = w.loy[j] = w.loz[j] = kInf;
+                w.hix[j] = w.hiy[j] = w.hiz[j] = -kInf;
+                w.child[j] = 0x7FFFFFFF;
+            }
+        }
+        out.nodes[size_t(t.wide)] = w;
+    }
+}
+
 }  // namespace omb

@@ -30,6 +30,25 @@ struct BuildResult {
     uint32_t depth = 0;
 };
 
+// The traversal's node: the binary tree collapsed to four children per node (boxes stored per axis, low planes and high
+// planes 16 bytes apart, so that a ray fetches its near and far planes by address from the sign of its direction).
+// child >= 0: inner node index; child < 0: leaf, ~child is the primitive reference; an empty slot has an inverted
+// box (lo = +INF, hi = -INF) that no ray enters.
+struct alignas(16) Node4 {
+    float lox[4], hix[4], loy[4], hiy[4], loz[4], hiz[4];
+    int32_t child[4];
+};
+static_assert(sizeof(Node4) == 112, "wide node must be 112 bytes");
+
+struct Wide4 {
+    std::vector<Node4> nodes;  // nodes[0] is the root when !nodes.empty()
+    uint32_t depth = 0;        // levels of wide nodes
+    uint32_t stack_need = 0;   // most entries a traversal can have on its stack: max over root-to-node paths of sum (children - 1)
+};
+// Collapses the binary tree: a node's children are the binary node's two children, then repeatedly the inner child
+// with the largest box is replaced by its own two children until there are `width` (2..4) of them.
+void collapse4(const BuildResult& in, Wide4& out, uint32_t width = 4);
+
 // refs[i] / boxes[i] describe primitive i.  Binned SAH, one primitive per leaf.
 void build(const std::vector<uint32_t>& refs, const std::vector<Aabb>& boxes, BuildResult& out);
 

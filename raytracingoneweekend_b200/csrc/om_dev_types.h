@@ -3,7 +3,7 @@
 // access is one LDS.128 / LDG.128.
 //
 //  hot image  (staged into shared memory by TMA bulk copy when it fits; else read from global/L2)
-//      BVH nodes 64 B | sphere world->local rows 48 B | cube world->local rows 48 B |
+//      BVH nodes 112 B (four children per node) | sphere world->local rows 48 B | cube world->local rows 48 B |
 //      triangle 64 B | infinite plane 32 B | parallelogram 64 B | always-test refs 4 B |
 //      marched sphere 16 B | marched box 32 B | marched torus 144 B | dyn marched 112 B + its program, 4 B per word |
 //      sphere material type 1 B
@@ -30,14 +30,15 @@ OMD_HD uint32_t ref_type(uint32_t ref) { return ref >> 28; }
 OMD_HD uint32_t ref_index(uint32_t ref) { return ref & 0x0FFFFFFFu; }
 
 // sizes in 16-byte units
-constexpr uint32_t U_NODE = 4, U_XF = 3, U_BARY = 4, U_PLANE = 2, U_MSPHERE = 1, U_MBOX = 2, U_MTORUS = 9, U_MDYN = 7, U_MAT = 2;
+constexpr uint32_t U_NODE = 4 /* binary node: distance BVH over the marched objects */, U_NODE4 = 7 /* traversal node, omb::Node4 */, U_XF = 3, U_BARY = 4, U_PLANE = 2, U_MSPHERE = 1, U_MBOX = 2, U_MTORUS = 9, U_MDYN = 7, U_MAT = 2;
 
 struct SceneHeader {
     uint32_t n[PT_COUNT];  // object count per PT_* type
-    uint32_t n_nodes;      // BVH inner nodes (0 = no BVH primitives)
+    uint32_t n_nodes;      // BVH nodes, four children each (0 = no BVH primitives)
     uint32_t n_large;      // refs in the always-test list (infinite planes, scene-sized objects)
     uint32_t n_bvh_prims;  // primitives reachable through the BVH
-    uint32_t bvh_depth;
+    uint32_t bvh_depth;    // levels of nodes
+    uint32_t stack_need;   // most entries a traversal can hold on its stack (omb::Wide4::stack_need)
     // hot image offsets, 16-byte units
     uint32_t off_nodes, off_hot[PT_COUNT], off_large;
     uint32_t hot_units;    // total size of the hot image

@@ -79,6 +79,7 @@ __device__ __forceinline__ float u32_to_f32(uint32_t u) { return (float)(u >> 8)
 __device__ __forceinline__ uint32_t sel4(uint32_t i, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     return i == 0u ? a : (i == 1u ? b : (i == 2u ? c : d));
 }
+__device__ __forceinline__ float sel4f(uint32_t i, float4 v) { return (i & 2u) ? ((i & 1u) ? v.w : v.z) : ((i & 1u) ? v.y : v.x); }
 // The next N (<= 4) draws of the stream, i.e. words draw .. draw+N-1 of the Philox block sequence
 // (word i lives in block i/4), with at most ONE block computation that every calling lane performs
 // together: the cached block serves the words before the next block boundary, the new block the
@@ -320,7 +321,45 @@ __device__ __forceinline__ float node_slab(float lx, float ly, float lz, float h
 }
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int STACK_DEPTH = 64;
+constexpr int STACK_DEPTH = 64;  // local-memory stack: om_scene.cpp collapses the tree so that SceneHeader::stack_need <= 60
+
+// ---- traversal stack ------------------------------------------------------------------------------------------------
+// An entry stands for a child of a wide node that the ray's box test hit but that was not the nearest: the child and the
+// entry distance, so that a pop can skip it once a closer hit is known.
+//  SHARED = true: 4-byte entries in shared memory behind the scene image, entry e of thread t at word e * STRIDE + t
+//    (conflict-free whatever the threads' depths are): {entry distance truncated to its upper 16 bits - never above the
+//    true value, so it only ever culls less -, node index (14 bits), child slot (2 bits)}; the child reference is read
+//    back from the node on the pop.  The host sizes the area from SceneHeader::stack_need and only picks this variant when
+//    it fits beside the scene and the tree has at most 16384 nodes.
+//  SHARED = false: {child, distance} pairs in local memory (scenes that live in global memory; the wavefront kernels).
+template <bool SHARED, int STRIDE>
+struct TravStack;
+template <int STRIDE>
+struct TravStack<true, STRIDE> {
+    uint32_t* col;
+    __device__ __forceinline__ void init(uint32_t hot_units) { col = reinterpret_cast<uint32_t*>(om_smem + hot_units) + threadIdx.x; }
+    __device__ __forceinline__ void push(int sp, uint32_t key, uint32_t node, int) { col[sp * STRIDE] = (key & 0xFFFF0003u) | (node << 2); }
+    template <bool SMEM>
+    __device__ __forceinline__ bool pop(int sp, float best_t, const SceneView<SMEM>& sv, const SceneHeader& S, int& cur) const {
+        const uint32_t e = col[sp * STRIDE];
+        if (!(__uint_as_float(e & 0xFFFF0000u) <= best_t)) return false;
+        cur = (int)sv.hot_word(S.off_nodes + omd::U_NODE4 * ((e >> 2) & 0x3FFFu) + 6u, e & 3u);
+        return true;
+    }
+};
+template <int STRIDE>
+struct TravStack<false, STRIDE> {
+    uint2 e[STACK_DEPTH];
+    __device__ __forceinline__ void init(uint32_t) {}
+    __device__ __forceinline__ void push(int sp, uint32_t key, uint32_t, int child) { e[sp] = make_uint2((uint32_t)child, key); }
+    template <bool SMEM>
+    __device__ __forceinline__ bool pop(int sp, float best_t, const SceneView<SMEM>&, const SceneHeader&, int& cur) const {
+        const uint2 x = e[sp];
+        if (!(__uint_as_float(x.y & 0xFFFFFFFCu) <= best_t)) return false;
+        cur = (int)x.x;
+        return true;
+    }
+};
 
 // k-th entry of the linear part of a query: the always-test list (infinite planes, scene-sized
 // objects), or in brute-force mode every traced primitive in the reference's scan order.
@@ -336,17 +375,61 @@ __device__ __forceinline__ uint32_t linear_ref(const SceneView<SMEM>& sv, const 
     return __float_as_uint(sel == 0 ? q.x : (sel == 1 ? q.y : (sel == 2 ? q.z : q.w)));
 }
 
+// One visit of a wide node (omb::Node4): the ray against the four child boxes.  The planes of each axis are fetched
+// near-first by address from the sign of the ray direction (fma is monotonic in the plane, so this is the min / max of
+// the two-plane form without computing it), every hit child gets the key {entry distance, slot} - one unsigned
+// compare orders them -, a five-exchange network sorts the four keys, the hit children but the nearest go on the stack
+// farthest first, and the nearest becomes `cur`.  Returns false when the ray misses all four.
+// The per-ray padding (SceneHeader::dyn_pad, see slab_padded) exists only in the global-memory variant.
+template <bool SMEM, class STK>
+__device__ __forceinline__ bool visit4(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t node, const RayInv& q, V3 o, float pad, float t_min, float best_t,
+                                       STK& stk, int& sp, int& cur) {
+    const uint32_t u = S.off_nodes + omd::U_NODE4 * node;
+    const uint32_t sx = __float_as_uint(q.inv.x) >> 31, sy = __float_as_uint(q.inv.y) >> 31, sz = __float_as_uint(q.inv.z) >> 31;
+    const float4 nx = sv.hot(u + sx), fx = sv.hot(u + (sx ^ 1u));
+    const float4 ny = sv.hot(u + 2u + sy), fy = sv.hot(u + 2u + (sy ^ 1u));
+    const float4 nz = sv.hot(u + 4u + sz), fz = sv.hot(u + 4u + (sz ^ 1u));
+    const float4 cf = sv.hot(u + 6u);
+    auto key = [&](float nxj, float fxj, float nyj, float fyj, float nzj, float fzj, uint32_t j) -> uint32_t {
+        float ax = fmaf(nxj, q.inv.x, q.noinv.x), bx = fmaf(fxj, q.inv.x, q.noinv.x);
+        float ay = fmaf(nyj, q.inv.y, q.noinv.y), by = fmaf(fyj, q.inv.y, q.noinv.y);
+        float az = fmaf(nzj, q.inv.z, q.noinv.z), bz = fmaf(fzj, q.inv.z, q.noinv.z);
+        bool real = true;
+        if (!SMEM && pad != 0.f) {
+            real = ax <= bx;  // an empty slot's inverted box (+INF, -INF) would pad to NaN planes, which fmaxf / fminf drop
+            const float dx = fmaxf(fabsf(nxj - o.x), fabsf(fxj - o.x)), dy = fmaxf(fabsf(nyj - o.y), fabsf(fyj - o.y)), dz = fmaxf(fabsf(nzj - o.z), fabsf(fzj - o.z));
+            const float e = pad * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+            const float ex = e * fabsf(q.inv.x), ey = e * fabsf(q.inv.y), ez = e * fabsf(q.inv.z);
+            ax -= ex; bx += ex; ay -= ey; by += ey; az -= ez; bz += ez;
+        }
+        const float tn = fmaxf(fmaxf(ax, ay), fmaxf(az, t_min));
+        const float tf = fminf(fminf(bx, by), fminf(bz, best_t));
+        return (real && tn <= tf) ? ((__float_as_uint(fmaxf(tn, 0.f)) & 0xFFFFFFFCu) | j) : 0xFFFFFFFFu;
+    };
+    uint32_t k0 = key(nx.x, fx.x, ny.x, fy.x, nz.x, fz.x, 0u), k1 = key(nx.y, fx.y, ny.y, fy.y, nz.y, fz.y, 1u);
+    uint32_t k2 = key(nx.z, fx.z, ny.z, fy.z, nz.z, fz.z, 2u), k3 = key(nx.w, fx.w, ny.w, fy.w, nz.w, fz.w, 3u);
+    auto cx = [](uint32_t& a, uint32_t& b) { const uint32_t lo = min(a, b), hi = max(a, b); a = lo; b = hi; };
+    cx(k0, k1); cx(k2, k3); cx(k0, k2); cx(k1, k3); cx(k1, k2);
+    if (k0 == 0xFFFFFFFFu) return false;
+    auto child = [&](uint32_t k) { return __float_as_int(sel4f(k & 3u, cf)); };
+    if (k3 != 0xFFFFFFFFu) { stk.push(sp, k3, node, child(k3)); sp++; }
+    if (k2 != 0xFFFFFFFFu) { stk.push(sp, k2, node, child(k2)); sp++; }
+    if (k1 != 0xFFFFFFFFu) { stk.push(sp, k1, node, child(k1)); sp++; }
+    cur = child(k0);
+    return true;
+}
+
 // FrozenHittableList::hit, traced part (hits.rs:270-286), for a whole warp at once.
 //
 // Every lane walks its own ray through a list of ITEMS: first the linear entries, then the BVH
-// (inner node = box pair, leaf = primitive).  A lane's next item is either an inner node or a
+// (inner node = four child boxes, leaf = primitive).  A lane's next item is either an inner node or a
 // leaf; each iteration the warp VOTES and runs only the kind that more lanes are waiting for, so
 // the two bodies always execute with at least half of the busy lanes active (the first version
 // tested a leaf the moment a lane reached it: ~2 lanes active, half of all issue slots).
 // All 32 lanes must call this; `alive` says whether the lane has a ray.
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool COUNT, class STK>
 __device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute,
-                                                    bool alive, Counters& cn, int2* stack) {
+                                                    bool alive, Counters& cn, STK& stk) {
     Best best;
     best.t = t_max;
     best.ref = omd::REF_NONE;
@@ -361,8 +444,7 @@ __device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, c
     auto pop = [&]() {
         while (sp > 0) {
             sp--;
-            const int2 e = stack[sp];
-            if (__int_as_float(e.y) <= best.t) { cur = e.x; return; }
+            if (stk.pop(sp, best.t, sv, S, cur)) return;
         }
         act = false;
     };
@@ -378,19 +460,8 @@ __device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, c
         if ((m_inner | m_leaf) == 0u) break;
         if (__popc(m_inner) >= __popc(m_leaf)) {
             if (act && cur >= 0) {
-                const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
-                const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
                 if (COUNT) cn.node_visits++;
-                const float tl = node_slab<SMEM>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, r.o, pad, t_min, best.t);
-                const float tr = node_slab<SMEM>(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, r.o, pad, t_min, best.t);
-                const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
-                if (tl < kInf && tr < kInf) {
-                    const bool right_first = tr < tl;
-                    if (sp < STACK_DEPTH) { stack[sp] = make_int2(right_first ? cl : cr, __float_as_int(right_first ? tl : tr)); sp++; }
-                    cur = right_first ? cr : cl;
-                } else if (tl < kInf) cur = cl;
-                else if (tr < kInf) cur = cr;
-                else pop();
+                if (!visit4(sv, S, (uint32_t)cur, q, r.o, pad, t_min, best.t, stk, sp, cur)) pop();
             }
         } else {
             if (act && cur < 0) {
@@ -548,7 +619,7 @@ __device__ __forceinline__ uint32_t marched_ref(const SceneHeader& S, uint32_t j
     if (!DYN || j < n_ms + n_mb + n_mt) return omd::make_ref(omd::PT_MTORUS, j - n_ms - n_mb);
     return omd::make_ref(omd::PT_MDYN, j - n_ms - n_mb - n_mt);  // marched_objects, after the typed lists (hits.rs:312-320)
 }
-constexpr int MSTACK = 40;  // scratch entries nearest_marched needs (<= STACK_DEPTH: the traversal stack is free by then)
+constexpr int MSTACK = 40;  // scratch entries nearest_marched_accel needs
 struct Near {
     uint32_t evals;  // SDFs evaluated (executed-work accounting)
     float d;       // min over the marched objects of |sdf(p)|
@@ -688,7 +759,8 @@ struct Hit {
 // picks: merely linking the structures' code into the kernel that renders C2 (one marched torus, never uses them) cost it
 // 8-10 % (more spill traffic in the 64-register main body), so that kernel does not contain it.
 template <bool SMEM, bool COUNT, bool ACCEL, bool DYN>
-__device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, Counters* cn, int2* stk) {
+__device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, Counters* cn) {
+    int2 stk[ACCEL ? MSTACK : 1];  // scratch of the distance-BVH walk
     Hit out;
     out.t = closest;
     out.ref = omd::REF_NONE;
@@ -740,9 +812,9 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
 // Warp-collective: all 32 lanes call it, `alive` marks the lanes that carry a ray.
 // MA: 0 = the scene has no candidate grid / distance BVH and no dyn marched objects, 1 = it has the structures,
 // 3 = it has dyn marched objects (om_dyn_marched), 2 = look at the header (parity hooks)
-template <bool SMEM, bool COUNT, int MA>
+template <bool SMEM, bool COUNT, int MA, class STK>
 __device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const SceneHeader& S, const Ray& r, float t_min, float t_max, bool brute, bool alive,
-                                                Counters& cn, int2* stack) {
+                                                Counters& cn, STK& stack) {
     if (COUNT && alive) cn.segments++;
     const Best b = closest_traced_warp<SMEM, COUNT>(sv, S, r, t_min, t_max, brute, alive, cn, stack);
     Hit h;
@@ -758,12 +830,12 @@ __device__ __forceinline__ Hit closest_hit_warp(const SceneView<SMEM>& sv, const
         const float te = slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, t_min, fminf(t_max, h.t));
         if (te < kInf) {
             auto run = [&]() -> Hit {
-                if constexpr (MA == 0) return march<SMEM, COUNT, false, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
-                else if constexpr (MA == 1) return march<SMEM, COUNT, true, false>(sv, S, r, t_min, t_max, h.t, &cn, stack);
-                else if constexpr (MA == 3) return march<SMEM, COUNT, false, true>(sv, S, r, t_min, t_max, h.t, &cn, stack);
-                else return S.n[omd::PT_MDYN] != 0u ? march<SMEM, COUNT, false, true>(sv, S, r, t_min, t_max, h.t, &cn, stack)
-                            : ((S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u ? march<SMEM, COUNT, true, false>(sv, S, r, t_min, t_max, h.t, &cn, stack)
-                                                                       : march<SMEM, COUNT, false, false>(sv, S, r, t_min, t_max, h.t, &cn, stack));
+                if constexpr (MA == 0) return march<SMEM, COUNT, false, false>(sv, S, r, t_min, t_max, h.t, &cn);
+                else if constexpr (MA == 1) return march<SMEM, COUNT, true, false>(sv, S, r, t_min, t_max, h.t, &cn);
+                else if constexpr (MA == 3) return march<SMEM, COUNT, false, true>(sv, S, r, t_min, t_max, h.t, &cn);
+                else return S.n[omd::PT_MDYN] != 0u ? march<SMEM, COUNT, false, true>(sv, S, r, t_min, t_max, h.t, &cn)
+                            : ((S.mgrid_dim[0] | S.n_mbvh_nodes) != 0u ? march<SMEM, COUNT, true, false>(sv, S, r, t_min, t_max, h.t, &cn)
+                                                                       : march<SMEM, COUNT, false, false>(sv, S, r, t_min, t_max, h.t, &cn));
             };
             const Hit m = run();
             if (m.ref != omd::REF_NONE) h = m;
@@ -1024,8 +1096,10 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
     const bool align = (A.flags & OM_RENDER_PHASE_ALIGN) != 0;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
     unsigned long long credited = 0, traced = 0;
+    uint32_t warp_iters = 0, lane_iters = 0;  // COUNT: lane occupancy of the path loop
     const uint32_t lane = threadIdx.x & 31u;
-    int2 stack[STACK_DEPTH];
+    TravStack<SMEM, RENDER_THREADS> stack;  // shared memory behind the scene image when the scene is staged, else local memory
+    stack.init(S.hot_units);
     const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;  // segment 0 + `for _i in 1..depth`
 #if OM_GROUP_TICKETS
     __shared__ unsigned grp_lock[PB_GROUPS], grp_next[PB_GROUPS], grp_left[PB_GROUPS];
@@ -1097,6 +1171,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         bool fresh = true;
         while (__any_sync(FULL, todo > 0u)) {
             const bool alive = todo > 0u;
+            if (COUNT) { warp_iters++; lane_iters += alive ? 1u : 0u; }
             if (align) phase_bar_count(1);
             if (alive && fresh) {
                 const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
@@ -1169,6 +1244,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
             for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
             if ((threadIdx.x & 31) == 0 && v[i]) atomicAdd(&A.counters[CTR_SEGMENTS + i], v[i]);
         }
+        unsigned long long li = lane_iters;
+        for (int o = 16; o > 0; o >>= 1) li += __shfl_xor_sync(0xffffffffu, li, o);
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&A.counters[CTR_WARP_ITERS], (unsigned long long)warp_iters); atomicAdd(&A.counters[CTR_LANE_ITERS], li); }
     }
 }
 
@@ -1183,7 +1261,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_primary(const __grid_constan
     sv.hot_g = A.hot_g;
     sv.cold_g = A.cold_g;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
-    int2 stack[STACK_DEPTH];
+    TravStack<SMEM, CTA_THREADS> stack;
+    stack.init(A.scene.hot_units);
     // warp-uniform trip count: closest_hit_warp is a warp-collective
     for (uint32_t base = blockIdx.x * CTA_THREADS; base < A.npx; base += gridDim.x * CTA_THREADS) {
         const uint32_t pxl = base + threadIdx.x;
@@ -1210,7 +1289,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) k_trace_rays(const __grid_cons
     sv.hot_g = A.hot_g;
     sv.cold_g = A.cold_g;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
-    int2 stack[STACK_DEPTH];
+    TravStack<SMEM, CTA_THREADS> stack;
+    stack.init(A.scene.hot_units);
     for (uint32_t base = blockIdx.x * CTA_THREADS; base < A.n; base += gridDim.x * CTA_THREADS) {
         const uint32_t i = base + threadIdx.x;
         const bool alive = i < A.n;

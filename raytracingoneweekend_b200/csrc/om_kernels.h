@@ -4,6 +4,9 @@
 
 #define OM_DECLARE_KERNELS(NS)                                                                                                     \
     namespace NS {                                                                                                                 \
+    /* shared-memory traversal stacks behind the staged scene image (TravStack<true, ..>): bytes per CTA of k_render / of the parity hooks */ \
+    size_t render_stack_bytes(uint32_t stack_need);                                                                                \
+    size_t hook_stack_bytes(uint32_t stack_need);                                                                                  \
     int render_occupancy(bool smem, bool count, size_t smem_bytes);                                                                \
     cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st);      \
     int wf_extend_occupancy(bool smem, bool count, size_t smem_bytes);                                                             \

@@ -25,6 +25,9 @@ static int scene_march_variant(const omk::RenderArgs& a) {
     return (a.scene.mgrid_dim[0] | a.scene.n_mbvh_nodes) != 0u ? 1 : 0;
 }
 
+size_t render_stack_bytes(uint32_t stack_need) { return size_t(stack_need) * 4u * RENDER_THREADS; }
+size_t hook_stack_bytes(uint32_t stack_need) { return size_t(stack_need) * 4u * CTA_THREADS; }
+
 // resident CTAs per SM of the render kernel for this configuration (the same for both MA instances: one launch bound)
 int render_occupancy(bool smem, bool count, size_t smem_bytes) {
     int n = 0;

@@ -443,21 +443,27 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
         if (!built && strstr(why, ": ")) return std::string(why);
     }
     if (!built) omb::build(refs, boxes, bvh);
-    h.n_nodes = uint32_t(bvh.nodes.size());
+    // the traversal walks the tree four children at a time (half the visits of the binary tree, same primitives tested)
+    omb::Wide4 wide;
+    omb::collapse4(bvh, wide, 4);
+    if (wide.stack_need > 60u) omb::collapse4(bvh, wide, 2);  // a degenerate tree: one sibling per level, as the binary traversal (depth <= 62)
+    h.n_nodes = uint32_t(wide.nodes.size());
     h.n_large = uint32_t(large.size());
     h.n_bvh_prims = uint32_t(refs.size());
-    h.bvh_depth = bvh.depth;
+    h.bvh_depth = wide.depth;
+    h.stack_need = wide.stack_need;
 
     lap(built ? "bvh (device)" : "bvh (host)");
+    if (timing) fprintf(stderr, "[freeze] binary nodes %zu depth %u -> wide nodes %zu depth %u stack_need %u\n", bvh.nodes.size(), bvh.depth, wide.nodes.size(), wide.depth, wide.stack_need);
     // ---- hot image ----------------------------------------------------------------------------
-    out.hot.reserve(16 * bvh.nodes.size() + 12 * (L.spheres.size() + L.cubes.size()) + 16 * (L.triangles.size() + L.parallelograms.size()) + 4096);
+    out.hot.reserve(28 * wide.nodes.size() + 12 * (L.spheres.size() + L.cubes.size()) + 16 * (L.triangles.size() + L.parallelograms.size()) + 4096);
     Packer hot(out.hot);
     h.off_nodes = hot.units();
-    for (const omb::Node& nd : bvh.nodes) {
-        hot.f4(nd.lmin[0], nd.lmin[1], nd.lmin[2], nd.lmax[0]);
-        hot.f4(nd.lmax[1], nd.lmax[2], nd.rmin[0], nd.rmin[1]);
-        hot.f4(nd.rmin[2], nd.rmax[0], nd.rmax[1], nd.rmax[2]);
-        hot.u4(uint32_t(nd.left), uint32_t(nd.right), 0u, 0u);
+    for (const omb::Node4& nd : wide.nodes) {
+        hot.f4(nd.lox[0], nd.lox[1], nd.lox[2], nd.lox[3]); hot.f4(nd.hix[0], nd.hix[1], nd.hix[2], nd.hix[3]);
+        hot.f4(nd.loy[0], nd.loy[1], nd.loy[2], nd.loy[3]); hot.f4(nd.hiy[0], nd.hiy[1], nd.hiy[2], nd.hiy[3]);
+        hot.f4(nd.loz[0], nd.loz[1], nd.loz[2], nd.loz[3]); hot.f4(nd.hiz[0], nd.hiz[1], nd.hiz[2], nd.hiz[3]);
+        hot.u4(uint32_t(nd.child[0]), uint32_t(nd.child[1]), uint32_t(nd.child[2]), uint32_t(nd.child[3]));
     }
     h.off_hot[PT_SPHERE] = hot.units();
     for (const om_sphere& s : L.spheres) hot.rows3(s.m_world_to_local);

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 2) k_wf_extend(const __grid_co
     const bool have_bvh = !brute && S.n_nodes > 0u;
     const bool have_marched = S.n_marched != 0u;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
-    int2 stack[STACK_DEPTH];
+    TravStack<false, WF_EXT_THREADS> stack;  // local memory: two CTAs per SM leave no room for a shared stack beside the scene
 
     uint32_t state = WS_FETCH;
     uint32_t slot = WF_NONE;  // the ray this lane is tracing
@@ -107,8 +107,7 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 2) k_wf_extend(const __grid_co
     auto pop = [&]() {
         while (sp > 0) {
             sp--;
-            const int2 e = stack[sp];
-            if (__int_as_float(e.y) <= best.t) { cur = e.x; state = cur >= 0 ? WS_INNER : WS_LEAF; return; }
+            if (stack.pop(sp, best.t, sv, S, cur)) { state = cur >= 0 ? WS_INNER : WS_LEAF; return; }
         }
         state = WS_FETCH;  // traversal over: retire the result, take the next ray
     };
@@ -185,24 +184,10 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 2) k_wf_extend(const __grid_co
                 } else state = WS_DONE;  // the queue is empty
             }
         } else if (c_in >= c_lf) {
-#pragma unroll 1
-            for (int rep = 0; rep < 2; rep++) {
-                if (state == WS_INNER) {
-                    const uint32_t u = S.off_nodes + omd::U_NODE * (uint32_t)cur;
-                    const float4 n0 = sv.hot(u), n1 = sv.hot(u + 1), n2 = sv.hot(u + 2), n3 = sv.hot(u + 3);
-                    if (COUNT) cn.node_visits++;
-                    const float tl = node_slab<SMEM>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, q, ray.o, S.dyn_pad, A.tmin, best.t);
-                    const float tr = node_slab<SMEM>(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, q, ray.o, S.dyn_pad, A.tmin, best.t);
-                    const int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
-                    if (tl < kInf && tr < kInf) {
-                        const bool right_first = tr < tl;
-                        if (sp < STACK_DEPTH) { stack[sp] = make_int2(right_first ? cl : cr, __float_as_int(right_first ? tl : tr)); sp++; }
-                        cur = right_first ? cr : cl;
-                        state = cur >= 0 ? WS_INNER : WS_LEAF;
-                    } else if (tl < kInf) { cur = cl; state = cur >= 0 ? WS_INNER : WS_LEAF; }
-                    else if (tr < kInf) { cur = cr; state = cur >= 0 ? WS_INNER : WS_LEAF; }
-                    else pop();
-                }
+            if (state == WS_INNER) {
+                if (COUNT) cn.node_visits++;
+                if (visit4(sv, S, (uint32_t)cur, q, ray.o, S.dyn_pad, A.tmin, best.t, stack, sp, cur)) state = cur >= 0 ? WS_INNER : WS_LEAF;
+                else pop();
             }
         } else {
             if (state == WS_LEAF) {

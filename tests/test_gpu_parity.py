@@ -498,7 +498,7 @@ def test_gpu_bvh_build_same_results(api, A, O, rtiow):
     so hits and images must not change by a bit."""
     fz = api.FrozenHittableList.generate("many_spheres", 5, 20000, flags=A.FREEZE_GPU_BVH)
     st = fz.stats()
-    assert st["bvh_nodes"] == st["bvh_prims"] - 1 and 10 < st["bvh_depth"] <= 60
+    assert (st["bvh_prims"] - 1) / 3 <= st["bvh_nodes"] <= st["bvh_prims"] - 1 and 5 < st["bvh_depth"] <= 60  # four children per node
     osc = oracle_scene_from(O, fz)
     rng = np.random.default_rng(4)
     o = np.tile(np.array([60, 12, 14], np.float32), (4000, 1))

@@ -77,14 +77,15 @@ def test_other_generators(api):
     assert (mats == 2).mean() >= 0.5
     fz = api.FrozenHittableList.generate("many_spheres", 5, 20000)
     st = fz.stats()
-    assert fz.counts()["spheres"] == 20001 and st["bvh_prims"] == 20000 and st["always_test"] == 1 and st["bvh_nodes"] == 19999
+    assert fz.counts()["spheres"] == 20001 and st["bvh_prims"] == 20000 and st["always_test"] == 1
+    assert 19999 / 3 <= st["bvh_nodes"] <= 19999  # four children per node (omb::collapse4): between (n - 1) / 3 and n - 1 nodes
     assert st["fits_smem"] == 0 and st["bvh_depth"] < 64
 
 
 def test_bvh_stats_of_rtiow(api):
     st = api.FrozenHittableList.generate("random_scene", 1).stats()
     assert st["always_test"] == 1                   # the r=1000 ground sphere is tested once per ray
-    assert st["bvh_nodes"] == st["bvh_prims"] - 1   # one primitive per leaf
+    assert (st["bvh_prims"] - 1) / 3 <= st["bvh_nodes"] <= st["bvh_prims"] - 1   # one primitive per leaf, up to four children per node
     assert st["fits_smem"] == 1 and st["device_bytes"] < 100 * 1024
 
 

@@ -11,5 +11,6 @@ print(fz.stats())
 r = api.Renderer(fz, bench.make_camera(api, aspect), api.render_params(W, H, a.spp, seed=1, flags=a.flags | A.RENDER_COUNTERS))
 r.launch(0); r.sync()
 c = r.perf_counters(); ms, _ = r.elapsed_ms()
+print("lane occupancy of the path loop", round(c["lane_iters"] / max(1, 32 * c["warp_iters"]), 4))
 print(a.workload, "ms", round(ms, 2), {k: round(v / c["traced"], 3) for k, v in c.items() if k not in ("traced", "credited") and isinstance(v, int)})
 r.close()
