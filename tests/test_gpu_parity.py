@@ -531,7 +531,7 @@ def test_gpu_bvh_build_same_results(api, A, O, rtiow):
 def test_large_bvh_equals_linear_scan(api, A, freeze_flags):
     fz = api.FrozenHittableList.generate("many_spheres", 7, 100000, flags=freeze_flags)
     st = fz.stats()
-    assert st["bvh_nodes"] == st["bvh_prims"] - 1 and st["bvh_depth"] <= 60
+    assert (st["bvh_prims"] - 1) / 3 <= st["bvh_nodes"] <= st["bvh_prims"] - 1 and st["bvh_depth"] <= 60  # four children per node
     rng = np.random.default_rng(14)
     n = 3000
     o = rng.uniform(-90, 90, (n, 3)).astype(np.float32); o[:, 1] = rng.uniform(0.2, 12.0, n)
