@@ -350,6 +350,17 @@ OM_API om_status om_render_read_rgb(om_render* r, uint8_t* host_rgb, size_t nbyt
  * 4 MODE_DEPTH_WEIGHTED_BLUR, 5 MODE_SHOW_IDS, 6 MODE_ID_WEIGHTED_BLUR (the 3x3 cross-weighted filters of
  * main.rs:219-343; they need width, height >= 3).  The SDL window itself is not part of this library. */
 OM_API om_status om_render_read_view(om_render* r, uint32_t mode, uint8_t* host_rgb, size_t nbytes);
+/* om_render_read_view without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same bytes out.  The device-side RGB image and the reduction words of modes 1 / 3
+ * live in one file-scope device array of OM_VIEW_NOALLOC_MAX_PIXELS * 3 + 256 bytes (6 MiB + 256 B) that every GPU
+ * which loads the library holds until the process exits; the call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  Images of more than OM_VIEW_NOALLOC_MAX_PIXELS pixels are rejected with OM_ERR_INVALID
+ * (use om_render_read_view).  All calls on one device share the array, and it keeps the previous call's contents (the
+ * call re-initialises what it reads): calls that overlap on the GPU - two handles on different streams of the same
+ * device - race; serialise them.  Synchronises the handle's stream.                                                    */
+#define OM_VIEW_NOALLOC_MAX_PIXELS 2097152u /* 2 Mi pixels: covers 1920 x 1080 */
+OM_API om_status om_render_read_view_noalloc(om_render* r, uint32_t mode, uint8_t* host_rgb, size_t nbytes);
 /* F12 of the viewer (surface.save_bmp, main.rs:473-476): 24-bit BMP of an RGB24 buffer.             */
 OM_API om_status om_write_bmp(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height);
 /* reset every pixel to Pixel::new() (render_thread.rs:47-50) and the counters to 0.           */

@@ -34,6 +34,7 @@ RENDER_NO_SMEM_SCENE = 1 << 4
 RENDER_COUNTERS = 1 << 5
 
 CHUNK_PIXELS = 2730  # main.rs:174-175
+VIEW_NOALLOC_MAX_PIXELS = 2097152  # OM_VIEW_NOALLOC_MAX_PIXELS
 
 
 def obj_id(type_tag: int, index: int) -> int:

@@ -53,6 +53,7 @@ PROTOTYPES = {
     "om_render_read_pixels": ("st", [vp, vp, sz]),
     "om_render_read_rgb": ("st", [vp, vp, sz]),
     "om_render_read_view": ("st", [vp, u32, vp, sz]),
+    "om_render_read_view_noalloc": ("st", [vp, u32, vp, sz]),
     "om_write_bmp": ("st", [C.c_char_p, vp, u32, u32]),
     "om_render_reset": ("st", [vp]),
     "om_render_primary": ("st", [vp, u32, u32, vp, vp, sz]),

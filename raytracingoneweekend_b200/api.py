@@ -378,6 +378,13 @@ class Renderer:
         _lib.call("om_render_read_view", self.h, mode, rgb.ctypes.data, rgb.nbytes)
         return rgb
 
+    def read_view_noalloc(self, mode, out=None):
+        """read_view through om_render_read_view_noalloc: fixed device scratch, no allocation in the library (no
+        counterpart in the reference; at most _abi.VIEW_NOALLOC_MAX_PIXELS pixels).  `out` lets the caller reuse a buffer."""
+        rgb = np.zeros((self.params.height, self.params.width, 3), np.uint8) if out is None else out
+        _lib.call("om_render_read_view_noalloc", self.h, mode, rgb.ctypes.data, rgb.nbytes)
+        return rgb
+
     def primary(self, mode=0, sample_index=0):
         ids = np.zeros(self.npx, np.uint64); t = np.zeros(self.npx, np.float32)
         _lib.call("om_render_primary", self.h, mode, sample_index, ids.ctypes.data, t.ctypes.data, self.npx)

@@ -777,6 +777,70 @@ om_status om_render_read_view(om_render* r, uint32_t mode, uint8_t* host_rgb, si
     return OM_OK;
 }
 
+// ---- om_render_read_view_noalloc ---------------------------------------------------------------------------------
+// The same refresh as om_render_read_view for callers that may not allocate (CUDA graph capture, tight serving loops):
+// the device-side RGB image and the three reduction words live in one file-scope device array instead of the handle's
+// staging block.  No counterpart in the reference.
+// Layout: bytes [0, 3 * npx) = the RGB24 image, the reduction words at OM_VIEW_NOALLOC_RED_OFFSET.  Every GPU that loads
+// the library holds the array (6 MiB + 256 B) until the process exits.  All calls on a device share it and it keeps the
+// last call's contents: the reduction words are re-initialised by k_view_red_init at the start of every call, the image
+// bytes are overwritten in full before they are read.  Calls that overlap on the GPU (two handles on different streams
+// of one device) race on it.
+constexpr size_t OM_VIEW_NOALLOC_RED_OFFSET = size_t(OM_VIEW_NOALLOC_MAX_PIXELS) * 3u;
+static __device__ __align__(256) unsigned char om_view_scratch[OM_VIEW_NOALLOC_RED_OFFSET + 256u];
+// device code may name the array directly
+__global__ void k_view_red_init() {
+    uint32_t* red = reinterpret_cast<uint32_t*>(om_view_scratch + OM_VIEW_NOALLOC_RED_OFFSET);
+    if (threadIdx.x == 0u) { red[0] = 1u; red[1] = 0u; red[2] = 0u; }  // max n starts at 1, no finite depth seen yet
+}
+namespace {
+// Host code needs the array's DEVICE address: in host code `om_view_scratch` is only a stand-in for the symbol.
+// Looked up once per device, with that device current.
+constexpr int OM_MAX_DEVICES = 64;
+std::mutex g_view_scratch_mu;
+unsigned char* g_view_scratch_addr[OM_MAX_DEVICES] = {nullptr};
+om_status view_scratch_on_device(int dev, unsigned char** out) {
+    if (dev < 0 || dev >= OM_MAX_DEVICES) return fail(OM_ERR_INVALID, "om_render_read_view_noalloc: device %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_view_scratch_mu);
+    if (!g_view_scratch_addr[dev]) {
+        CU(cudaSetDevice(dev));
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, om_view_scratch);
+        if (e != cudaSuccess || !p) return fail(OM_ERR_CUDA, "om_render_read_view_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        g_view_scratch_addr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_view_scratch_addr[dev];
+    return OM_OK;
+}
+}  // namespace
+
+om_status om_render_read_view_noalloc(om_render* r, uint32_t mode, uint8_t* host_rgb, size_t nbytes) {
+    if (!r || !host_rgb) return fail(OM_ERR_INVALID, "om_render_read_view_noalloc: NULL argument");
+    if (mode > 6u) return fail(OM_ERR_INVALID, "om_render_read_view_noalloc: mode must be 0..6 (main.rs:361-368)");
+    if (nbytes != size_t(r->npx) * 3u) return fail(OM_ERR_INVALID, "om_render_read_view_noalloc: nbytes must be width*height*3");
+    if (r->npx > OM_VIEW_NOALLOC_MAX_PIXELS)
+        return fail(OM_ERR_INVALID, "om_render_read_view_noalloc: %u pixels exceed the fixed scratch of OM_VIEW_NOALLOC_MAX_PIXELS = %u (use om_render_read_view)",
+                    r->npx, (unsigned)OM_VIEW_NOALLOC_MAX_PIXELS);
+    if ((mode == 2u || mode == 4u || mode == 6u) && (r->p.width < 3u || r->p.height < 3u))
+        return fail(OM_ERR_INVALID, "om_render_read_view_noalloc: the 3x3 filters need an image of at least 3x3 (the reference's border loops, main.rs:324-342)");
+    CU(cudaSetDevice(r->dev));
+    unsigned char* scratch = nullptr;
+    const om_status s = view_scratch_on_device(r->dev, &scratch);
+    if (s != OM_OK) return s;
+    uint32_t* red = reinterpret_cast<uint32_t*>(scratch + OM_VIEW_NOALLOC_RED_OFFSET);
+    k_view_red_init<<<1, 32, 0, r->stream>>>();
+    CU(cudaGetLastError());
+    if (mode == 1u || mode == 3u) {
+        k_view_reduce<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, red);
+        CU(cudaGetLastError());
+    }
+    k_view<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, scratch, r->p.width, r->p.height, mode, red);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(host_rgb, scratch, nbytes, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return OM_OK;
+}
+
 om_status om_write_bmp(const char* path, const uint8_t* rgb, uint32_t width, uint32_t height) {
     if (!path || !rgb || !width || !height) return fail(OM_ERR_INVALID, "om_write_bmp: bad argument");
     FILE* f = fopen(path, "wb");

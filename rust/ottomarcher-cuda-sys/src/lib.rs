@@ -116,6 +116,8 @@ extern "C" {
     pub fn om_render_read_pixels(r: *mut om_render, host: *mut om_pixel, n: usize) -> om_status;
     pub fn om_render_read_rgb(r: *mut om_render, host_rgb: *mut u8, nbytes: usize) -> om_status;
     pub fn om_render_read_view(r: *mut om_render, mode: u32, host_rgb: *mut u8, nbytes: usize) -> om_status;
+    /// no counterpart in the reference; fixed device scratch, at most OM_VIEW_NOALLOC_MAX_PIXELS (2 097 152) pixels
+    pub fn om_render_read_view_noalloc(r: *mut om_render, mode: u32, host_rgb: *mut u8, nbytes: usize) -> om_status;
     pub fn om_write_bmp(path: *const c_char, rgb: *const u8, width: u32, height: u32) -> om_status;
     pub fn om_render_reset(r: *mut om_render) -> om_status;
     pub fn om_render_primary(r: *mut om_render, mode: u32, sample_index: u32, ids: *mut u64, t: *mut f32, n: usize) -> om_status;
