@@ -220,7 +220,14 @@ enum {
      * library picks: on for scenes that march 1-8 objects without a distance BVH (measured on B200:
      * C1 +29 %, C2 +6 %, C4 +5 %), off otherwise (spheres only -13 %, 65 marched objects -33 %).         */
     OM_RENDER_PHASE_ALIGN = 1u << 7,
-    OM_RENDER_NO_PHASE_ALIGN = 1u << 8
+    OM_RENDER_NO_PHASE_ALIGN = 1u << 8,
+    /* the CTA-resident wavefront ("path pool", csrc/om_pool.cuh): every CTA keeps a pool of path slots in shared memory
+     * beside the scene image and alternates an extend phase (BVH traversal of compacted rays) with a shade phase that
+     * takes the resolved rays one KIND at a time (marching, hit on a Lambertian / metal / dielectric sphere, other
+     * primitive, miss), so scatter, Stats::add and the next camera ray run with full warps.  The iterative-queue form
+     * of ray_color's recursion (render_thread.rs:128-143) without leaving the SM.  Needs the scene image, the traversal
+     * stacks and the pool to fit shared memory (else OM_ERR_INVALID) and max_depth < 65536.  Bit-identical output.   */
+    OM_RENDER_POOL = 1u << 9
 };
 
 typedef struct om_render_params {
@@ -250,6 +257,9 @@ typedef struct om_render om_render; /* the N render threads + their shared Vec<P
 
 /* ------------------------------------------------------------------------------------------ */
 /* scene: HittableList (hits.rs:37-43) — one list per concrete type, `world += &obj` ≙ add_*   */
+/* Lifetime: an om_render handle refers to its scene's device images for as long as it lives (the Rust side holds the
+ * FrozenHittableList in an Arc, main.rs:197-204).  While any handle created from a scene exists, om_scene_freeze,
+ * om_scene_clear and om_scene_destroy on that scene fail with OM_ERR_INVALID and change nothing: destroy the handles first. */
 OM_API om_status om_scene_create(om_scene** out);                 /* HittableList::new hits.rs:72 */
 OM_API om_status om_scene_clear(om_scene* s);                     /* HittableList::clear hits.rs:81 */
 OM_API om_status om_scene_destroy(om_scene* s);                   /* NULL is fine                */

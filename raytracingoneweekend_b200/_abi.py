@@ -28,6 +28,7 @@ RENDER_WAVEFRONT = 1 << 3
 RENDER_PERSISTENT = 1 << 6
 RENDER_PHASE_ALIGN = 1 << 7
 RENDER_NO_PHASE_ALIGN = 1 << 8
+RENDER_POOL = 1 << 9
 FREEZE_NO_ALWAYS_LIST, FREEZE_RAY_PADDING, FREEZE_STATIC_PADDING, FREEZE_NO_MARCHED_BVH = 1, 2, 4, 8
 FREEZE_GPU_BVH = 16
 RENDER_NO_SMEM_SCENE = 1 << 4

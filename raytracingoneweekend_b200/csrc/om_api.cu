@@ -8,6 +8,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <new>
@@ -148,6 +149,9 @@ struct om_scene {
     oms::FrozenScene fz;
     std::mutex mu;
     std::map<int, DevScene> dev;  // uploaded images per device
+    // live om_render handles: each keeps raw pointers into `dev` and re-reads fz.hdr at every launch, so the scene may not be
+    // re-frozen, cleared or destroyed under them (om_scene_freeze / _clear / _destroy return OM_ERR_INVALID while this is > 0)
+    std::atomic<int> handles{0};
     ~om_scene() { release_device(); }
     void release_device() {
         for (auto& kv : dev) {
@@ -173,6 +177,9 @@ om_status scene_on_device(om_scene* s, int dev, DevScene& out) {
     CU(cudaMalloc(&d.cold, s->fz.cold.size() * sizeof(float)));
     CU(cudaMemcpy(d.hot, s->fz.hot.data(), s->fz.hot.size() * sizeof(float), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d.cold, s->fz.cold.data(), s->fz.cold.size() * sizeof(float), cudaMemcpyHostToDevice));
+    // a pageable-memory cudaMemcpy may return once the data sits in the driver's staging buffer; the render streams are
+    // non-blocking (no implicit order with the legacy stream), so wait for the DMA itself before anyone launches on the image
+    CU(cudaDeviceSynchronize());
     s->dev[dev] = d;
     out = d;
     return OM_OK;
@@ -205,9 +212,14 @@ om_status om_scene_create(om_scene** out) {
     *out = new (std::nothrow) om_scene();
     return *out ? OM_OK : fail(OM_ERR_OOM, "om_scene_create: out of host memory");
 }
-om_status om_scene_destroy(om_scene* s) { delete s; return OM_OK; }
+om_status om_scene_destroy(om_scene* s) {
+    if (s && s->handles.load() > 0) return fail(OM_ERR_INVALID, "om_scene_destroy: %d render handle(s) still use this scene (om_render_destroy them first)", s->handles.load());
+    delete s;
+    return OM_OK;
+}
 om_status om_scene_clear(om_scene* s) {
     if (!s) return fail(OM_ERR_INVALID, "om_scene_clear: NULL scene");
+    if (s->handles.load() > 0) return fail(OM_ERR_INVALID, "om_scene_clear: %d render handle(s) still use this scene (om_render_destroy them first)", s->handles.load());
     s->lists = omh::SceneLists();
     s->frozen = false;
     s->release_device();
@@ -298,6 +310,7 @@ om_status om_scene_generate(om_scene* s, uint32_t kind, uint64_t seed, uint64_t 
 }
 om_status om_scene_freeze(om_scene* s, const om_camera* cam, uint32_t flags) {
     if (!s) return fail(OM_ERR_INVALID, "om_scene_freeze: NULL scene");
+    if (s->handles.load() > 0) return fail(OM_ERR_INVALID, "om_scene_freeze: %d render handle(s) still use this scene (om_render_destroy them first)", s->handles.load());
     s->release_device();
     s->frozen = false;
     const std::string err = oms::freeze(s->lists, cam, flags, s->fz);

@@ -279,6 +279,9 @@ struct om_render {
     omk::WfArgs wf;               // device arrays; n_slots == 0: not allocated
     int wf_grid_extend = 0, wf_grid_small = 0;
     bool wf_smem = false;
+    bool use_pool = false;       // OM_RENDER_POOL: k_render_pool instead of k_render
+    size_t pool_smem_bytes = 0;  // scene image + traversal stacks + slot pool + queues
+    int pool_grid = 0;
     uint32_t* wf_host_ctr = nullptr;  // pinned: wf::G_WORDS words per in-flight batch (2 batches)
     cudaEvent_t wf_ev[2] = {nullptr, nullptr};
     uint32_t n_uniform = 0;       // samples every live pixel has after the launches so far
@@ -370,6 +373,7 @@ om_status om_render_destroy(om_render* r) {
     for (int i = 0; i < 2; i++) if (r->wf_ev[i]) cudaEventDestroy(r->wf_ev[i]);
     if (r->own_stream) cudaStreamDestroy(r->own_stream);
     cudaSetDevice(prev);
+    if (r->scene) r->scene->handles.fetch_sub(1);
     delete r;
     return OM_OK;
 }
@@ -391,10 +395,11 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
     if (st != OM_OK) return st;
     om_render* r = new (std::nothrow) om_render();
     if (!r) return fail(OM_ERR_OOM, "om_render_create: out of host memory");
-    r->scene = const_cast<om_scene*>(frozen);
     r->cam = *cam;
     r->p = p;
     if ((p.flags & OM_RENDER_WAVEFRONT) && (p.flags & OM_RENDER_PERSISTENT)) { delete r; return fail(OM_ERR_INVALID, "om_render_create: OM_RENDER_WAVEFRONT and OM_RENDER_PERSISTENT exclude each other"); }
+    r->scene = const_cast<om_scene*>(frozen);
+    r->scene->handles.fetch_add(1);  // released by om_render_destroy (also on the failure paths below)
     r->dev = dev;
     memset(&r->wf, 0, sizeof r->wf);
     r->npx = p.width * p.height;
@@ -445,6 +450,17 @@ om_status om_render_create(om_render** out, const om_scene* frozen, const om_cam
             return fail(OM_ERR_CUDA, "render kernel cannot be resident on device %d (%s)", dev, cudaGetErrorString(e));
         }
         r->grid = occ * r->props.sms;
+        if (p.flags & OM_RENDER_POOL) {
+            if (p.flags & OM_RENDER_WAVEFRONT) return fail(OM_ERR_INVALID, "om_render_create: OM_RENDER_POOL and OM_RENDER_WAVEFRONT exclude each other");
+            r->pool_smem_bytes = hot_bytes + (exact ? om_exact::pool_extra_smem(stack_need) : om_fast::pool_extra_smem(stack_need));
+            const bool fits = may_stage && small_tree && p.max_depth < 65536u && r->pool_smem_bytes + 1024u <= r->props.smem_optin;
+            const int o3 = fits ? (exact ? om_exact::pool_occupancy(count, r->pool_smem_bytes) : om_fast::pool_occupancy(count, r->pool_smem_bytes)) : 0;
+            if (o3 < 1) return fail(OM_ERR_INVALID, "om_render_create: OM_RENDER_POOL needs the scene image, the stacks and the path pool in shared memory (%zu bytes wanted, %zu available)",
+                                    r->pool_smem_bytes, r->props.smem_optin);
+            r->use_pool = true;
+            r->pool_grid = o3 * r->props.sms;
+            r->p.flags |= OM_RENDER_PERSISTENT;  // (not the global wavefront; the automatic choices below do not apply)
+        }
         if (!(p.flags & (OM_RENDER_WAVEFRONT | OM_RENDER_PERSISTENT))) {  // automatic choice (see OM_RENDER_PERSISTENT)
             const bool fits = hot_bytes + om_exact::wf_stage_bytes() + 1024u <= r->props.smem_optin / 2;
             // many marched objects without a distance BVH: long SDF loops stall the persistent kernel's warps
@@ -597,6 +613,7 @@ namespace {
 // later launches of the handle.  Same pixels in any order (the passes of a handle are bit-identical to one launch).
 bool can_order_blocks(const om_render* r) {
     if (r->p.flags & (OM_RENDER_WAVEFRONT | OM_RENDER_ADAPTIVE)) return false;
+    if (r->use_pool) return false;  // the pool hands out pixels one by one: nothing to order
     if (r->p.part_world > 1u || r->owners || getenv("OM_NO_BLOCK_ORDER")) return false;
     const uint32_t tiles_x = (r->p.width + 7u) / 8u, tiles_y = (r->p.height + 3u) / 4u;
     return ((tiles_x + 1u) / 2u) * ((tiles_y + 3u) / 4u) >= 8u * (uint32_t)r->props.sms;
@@ -669,8 +686,10 @@ om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
         om_status s = run_wavefront(r, a, n_target);
         if (s != OM_OK) { r->pool.push_back(ev); return s; }
     } else {
-        cudaError_t e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
-                              : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+        cudaError_t e;
+        if (r->use_pool) e = exact ? om_exact::launch_render_pool(a, count, r->pool_grid, r->pool_smem_bytes, r->stream) : om_fast::launch_render_pool(a, count, r->pool_grid, r->pool_smem_bytes, r->stream);
+        else e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
+                       : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
         if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
         r->kernels++;
     }

@@ -5,5 +5,6 @@
 #include "om_device.cuh"
 namespace OM_NS {
 #include "om_wavefront.cuh"
+#include "om_pool.cuh"
 }
 #include "om_launch.inl"

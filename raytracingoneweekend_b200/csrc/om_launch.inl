@@ -60,6 +60,31 @@ cudaError_t launch_trace(const omk::TraceArgs& a, bool smem, int grid, size_t sm
     return cudaGetLastError();
 }
 
+// ---- CTA-resident wavefront (om_pool.cuh) ----
+size_t pool_extra_smem(uint32_t stack_need) { return pool_extra_bytes(stack_need); }
+template <class F>
+static void with_pool_kernel(bool count, int ma, F f) {
+    if (count) { if (ma == 1) f(k_render_pool<true, 1>); else if (ma == 3) f(k_render_pool<true, 3>); else f(k_render_pool<true, 0>); }
+    else { if (ma == 1) f(k_render_pool<false, 1>); else if (ma == 3) f(k_render_pool<false, 3>); else f(k_render_pool<false, 0>); }
+}
+int pool_occupancy(bool count, size_t smem_bytes) {
+    int n = 0;
+    cudaError_t e = cudaSuccess;
+    with_pool_kernel(count, 0, [&](auto kern) {
+        e = prep(kern, smem_bytes);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, POOL_T, smem_bytes);
+    });
+    if (e != cudaSuccess) cudaGetLastError();
+    return e == cudaSuccess ? n : 0;
+}
+cudaError_t launch_render_pool(const omk::RenderArgs& a, bool count, int grid, size_t smem_bytes, cudaStream_t st) {
+    with_pool_kernel(count, scene_march_variant(a), [&](auto kern) {
+        prep(kern, smem_bytes);
+        kern<<<grid, POOL_T, smem_bytes, st>>>(a);
+    });
+    return cudaGetLastError();
+}
+
 // ---- wavefront pipeline (om_wavefront.cuh) ----
 size_t wf_stage_bytes() { return WF_STAGE_BYTES; }
 int wf_extend_occupancy(bool smem, bool count, size_t scene_bytes) {

@@ -177,16 +177,18 @@ def test_full_resolution_pipelines_agree_bit_for_bit(api, A, kind, seed, n_param
     fz = api.FrozenHittableList.generate(kind, seed, n_param)
     cam = api.Camera.new((13, 2, 3) if kind != "many_spheres" else (60, 12, 14), (0, 0, 0), (0, 1, 0), 20.0, W / H, 0.1, 10.0)
     out = []
-    for fl in (A.RENDER_PERSISTENT, A.RENDER_WAVEFRONT):
+    pipelines = [A.RENDER_PERSISTENT, A.RENDER_WAVEFRONT] + ([A.RENDER_POOL] if kind != "many_spheres" else [])  # the pool needs the scene in shared memory
+    for fl in pipelines:
         r = api.Renderer(fz, cam, api.render_params(W, H, spp, seed=17, flags=fl))
         r.launch(0); r.sync()
         px = r.read_pixels()
         out.append((px, r.samples_done(), r.samples_traced()))
         r.close()
-    a, b = out
+    a = out[0]
     assert (a[0]["n"] == spp).all() and a[1] == a[2] == W * H * spp
-    assert a[1:] == b[1:]
-    for f in ("sum", "avg_depth"):
-        assert (a[0][f].view(np.uint32) == b[0][f].view(np.uint32)).all(), f
-    for f in ("n", "bad_avgs", "bloom", "color"):
-        assert (a[0][f] == b[0][f]).all(), f
+    for b in out[1:]:
+        assert a[1:] == b[1:]
+        for f in ("sum", "avg_depth"):
+            assert (a[0][f].view(np.uint32) == b[0][f].view(np.uint32)).all(), f
+        for f in ("n", "bad_avgs", "bloom", "color"):
+            assert (a[0][f] == b[0][f]).all(), f

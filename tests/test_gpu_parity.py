@@ -342,6 +342,51 @@ def test_wavefront_bit_exact_adaptive_multipass_and_marched(api, A, rtiow, mixed
     r.close()
 
 
+# ---- CTA-resident wavefront (OM_RENDER_POOL, csrc/om_pool.cuh): same bits as the oracle ----
+@pytest.mark.parametrize("W,H,spp,depth,flags_extra", [(64, 48, 6, 50, 0), (37, 23, 5, 50, 0), (2, 2, 3, 50, 0), (48, 32, 4, 1, 0), (40, 30, 3, 3, 0), (64, 48, 6, 50, 4)])
+def test_pool_bit_exact_fixed_spp(api, A, rtiow, W, H, spp, depth, flags_extra):
+    fz, osc = rtiow
+    cam = cam_rtiow(api, W / H)
+    r = api.Renderer(fz, cam, api.render_params(W, H, spp, max_depth=depth, seed=21, flags=A.RENDER_POOL | flags_extra))
+    r.launch(0); r.sync()
+    ref = osc.render(cam, api.render_params(W, H, spp, max_depth=depth, seed=21, flags=0))
+    assert_pixels_equal(r.read_pixels(), ref["pixels"])
+    assert r.samples_done() == ref["credited"] == W * H * spp and r.samples_traced() == ref["traced"]
+    r.close()
+
+
+def test_pool_bit_exact_adaptive_multipass_marched_and_limits(api, A, rtiow, mixed, O):
+    fz, osc = rtiow
+    cam = cam_rtiow(api, 1.5)
+    r = api.Renderer(fz, cam, api.render_params(60, 40, 40, seed=4, flags=A.RENDER_ADAPTIVE | A.RENDER_POOL))
+    for _ in range(5):
+        r.launch(8)
+    r.sync()
+    ref = osc.render(cam, api.render_params(60, 40, 40, seed=4, flags=A.RENDER_ADAPTIVE))
+    assert_pixels_equal(r.read_pixels(), ref["pixels"])
+    assert r.samples_done() == ref["credited"] and r.samples_traced() == ref["traced"]
+    r.close()
+    fzx, oscx = mixed   # every primitive type, marched objects in front of traced ones
+    camx = api.Camera.new((6, 3, 7), (0, 0.5, 0), (0, 1, 0), 40.0, 1.5, 0.05, 9.0)
+    r = api.Renderer(fzx, camx, api.render_params(48, 32, 4, seed=2, flags=A.RENDER_POOL)); r.launch(0); r.sync()
+    assert_pixels_equal(r.read_pixels(), oscx.render(camx, api.render_params(48, 32, 4, seed=2))["pixels"])
+    r.close()
+    fzm = api.FrozenHittableList.generate("marched", 3)   # 65 marched objects: marches span many phases
+    oscm = oracle_scene_from(O, fzm)
+    r = api.Renderer(fzm, cam_rtiow(api, 4 / 3), api.render_params(32, 24, 2, seed=2, flags=A.RENDER_POOL)); r.launch(0); r.sync()
+    assert_pixels_equal(r.read_pixels(), oscm.render(cam_rtiow(api, 4 / 3), api.render_params(32, 24, 2, seed=2))["pixels"])
+    r.close()
+    # what does not fit shared memory is refused, not silently rendered by something else
+    big = api.FrozenHittableList.generate("many_spheres", 5, 20000)
+    for bad in (dict(flags=A.RENDER_POOL), ):
+        with pytest.raises(api.OmError) as e:
+            api.Renderer(big, cam, api.render_params(16, 16, 1, **bad))
+        assert e.value.status == A.OM_ERR_INVALID
+    with pytest.raises(api.OmError) as e:
+        api.Renderer(fz, cam, api.render_params(16, 16, 1, flags=A.RENDER_POOL | A.RENDER_WAVEFRONT))
+    assert e.value.status == A.OM_ERR_INVALID
+
+
 @pytest.mark.parametrize("kind,seed", [("random_scene", 1), ("glass_heavy", 4), ("marched", 3)])
 def test_wavefront_equals_persistent_kernel_large(api, A, kind, seed):
     """At a size the oracle cannot reach in seconds (more pixels than slots are exercised by the
