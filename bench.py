@@ -1,19 +1,23 @@
 #!/usr/bin/env python
 """Headline benchmark: Msamples/s of the per-pixel path-trace / ray-march hot path.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C2]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C2] [--adaptive]
 
 One "step" = one full render of the workload (every pixel, every sample) through
 render_thread::render's replacement.  Default workload = BASELINE.json configs[1]: the RTIOW
 random_scene (main.rs:37-100) at 1920x1080, 1024 spp, depth 50 (fixed spp).  With N > 1 (torchrun,
 one rank per GPU) the SAME job is split into spp slices and combined by one NCCL reduce: strong
-scaling.  Prints ONE JSON line on rank 0.
+scaling.  --adaptive runs the reference's own mode instead (a pixel retires when its 8-bit colour
+stood still for five samples, render_thread.rs:23-39,194-200; interleaved 2730-pixel chunks over
+the ranks, main.rs:172-189).  Prints ONE JSON line on rank 0.
 """
 import argparse
 import json
 import os
+import pickle
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -31,15 +35,17 @@ WORKLOADS = {
     "C4": ("glass_heavy", 4, 0, 3840, 2160, 512, 16.0 / 9.0),
     "C5": ("many_spheres", 5, 1000000, 3840, 2160, 64, 16.0 / 9.0),
 }
+LOOKFROM = {"many_spheres": (60, 12, 14)}  # C5's camera is pulled back; everything else uses main.rs:136-142
 MAX_DEPTH, TMIN, TMAX = 50, 0.001, 100.0  # main.rs:146,205-206
-# DRAM bytes per k_render launch measured with ncu, keyed by (workload, spp per launch, GPUs, wavefront)
-NCU_DRAM_BYTES = {("C2", 1024, 1, False): 121891584 + 557661952}  # profiles/r1_v1e_c2_1024spp_dram.csv
-# ncu --set full of k_render on C2 (16-spp launch, profiles/r1_v1g_c2_k_render.txt): what the FP32 figure does not show
-NCU_K_RENDER_C2 = {"source": "profiles/r1_v1g_c2_k_render.txt", "issue_active_pct": 65.1, "pipe_fma_cycles_active_pct": 22.2, "inst_executed_pipe_alu_pct": 53.1,
-                   "threads_per_warp_instruction": 13.2, "stall_barrier_per_issue": 3.22, "stall_no_instruction_per_issue": 0.40}
+# ncu figures of the dominant kernel per workload, written by tools/ncu_to_json.py from captures of THIS tree (no constants here)
+NCU_FILE = os.path.join(ROOT, "profiles", "ncu_current.json")
 
-# flops "as the reference executes it" per executed unit of work
-FLOPS = dict(raygen=73, accumulate=20, node_visit=48, prim_test=61, sdf_eval=56, normal_eval=210, shade=50)
+# flops "as the reference executes it" per executed unit of work.  A node visit of the four-wide BVH tests
+# four child boxes (4 x 24 flop slab tests).
+FLOPS = dict(raygen=73, accumulate=20, node_visit=96, prim_test=61, sdf_eval=56, normal_eval=210, shade=50)
+# bytes a traversal step fetches (scenes larger than shared memory, SURVEY 8(d) "C5"): 112-byte node, 48-byte world->local rows
+# per primitive test, and per resolved hit the 48-byte local->world rows + 32-byte material record
+BYTES = dict(node_visit=112, prim_test=48, hit=80)
 
 
 _OUT = sys.stdout
@@ -50,6 +56,19 @@ def flops_per_sample(c, samples):
     s = float(samples)
     return (FLOPS["raygen"] + FLOPS["accumulate"] + (c["segments"] * FLOPS["shade"] + c["node_visits"] * FLOPS["node_visit"]
             + c["prim_tests"] * FLOPS["prim_test"] + c["sdf_evals"] * FLOPS["sdf_eval"] + c["normal_evals"] * FLOPS["normal_eval"]) / s)
+
+
+def bytes_per_sample(c, samples, spp):
+    s = float(samples)
+    return (c["node_visits"] * BYTES["node_visit"] + c["prim_tests"] * BYTES["prim_test"] + c["segments"] * BYTES["hit"]) / s + 64.0 / spp
+
+
+def load_ncu(workload):
+    try:
+        with open(NCU_FILE) as f:
+            return json.load(f).get(workload)
+    except (OSError, ValueError):
+        return None
 
 
 class ClockSampler:
@@ -86,34 +105,61 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def make_camera(api, aspect):
-    return api.Camera.new((13, 2, 3), (0, 0, 0), (0, 1, 0), 20.0, aspect, 0.1, 10.0)  # main.rs:136-142
+def make_camera(api, aspect, kind=None):
+    return api.Camera.new(LOOKFROM.get(kind, (13, 2, 3)), (0, 0, 0), (0, 1, 0), 20.0, aspect, 0.1, 10.0)  # main.rs:136-142
 
 
-def oracle_scene_from(frozen):
+# ---- the reference arm: oracle only ---------------------------------------------------------------------------------------
+_DUMP = """
+import pickle, sys
+sys.path.insert(0, %r)
+from raytracingoneweekend_b200 import api
+fz = api.FrozenHittableList.generate(%r, %d, %d)
+pickle.dump({k: bytes(v) for k, v in fz.lists().items()}, open(sys.argv[1], "wb"))
+"""
+
+
+def oracle_scene_for(kind, seed, n_param):
+    """The workload's scene inside the oracle, WITHOUT loading the product library into this process: random_scene comes from
+    the oracle's own generator (oracle/ref_render.hpp, restating main.rs:37-100); the synthetic benchmark scenes exist only in
+    the product's generator, so a child process makes them and hands them over as data."""
     from oracle import binding as B
+    from raytracingoneweekend_b200 import _abi as A  # ctypes struct definitions only: loads nothing
+    if kind == "random_scene":
+        return B.OracleScene().random_scene(seed)
+    with tempfile.NamedTemporaryFile(suffix=".pkl") as tmp:
+        subprocess.check_call([sys.executable, "-c", _DUMP % (ROOT, kind, seed, n_param), tmp.name], stdout=subprocess.DEVNULL)
+        lists = pickle.load(open(tmp.name, "rb"))
+    types = {"spheres": A.Sphere, "cubes": A.Cube, "triangles": A.Barycentric, "infinite_planes": A.InfinitePlane, "parallelograms": A.Barycentric,
+             "marched_spheres": A.MarchedSphere, "marched_boxes": A.MarchedBox, "marched_tori": A.MarchedTorus}
     o = B.OracleScene()
-    for k, arr in frozen.lists().items():
-        o.add(k, arr)
+    for k, raw in lists.items():
+        T = types[k]
+        n = len(raw) // __import__("ctypes").sizeof(T)
+        if n:
+            o.add(k, (T * n).from_buffer_copy(raw))
     return o
 
 
-def cpu_reference_rate(api, wl, seconds_target=10.0, threads=0):
-    """The reference's CPU algorithm (oracle port: brute-force hit(), num_cpus-1 threads, 2730-pixel
-    chunks) on a bounded sample of the workload: every `world`-th chunk at 1 spp.  Returns
-    (Msamples/s, threads, description)."""
+def cpu_reference_rate(wl, seconds_target=10.0, threads=0, osc=None):
+    """The reference's CPU algorithm (oracle port: brute-force hit(), num_cpus-1 threads, 2730-pixel chunks, main.rs:170-189) on a
+    bounded sample of the workload: every `world`-th chunk at 1 spp (samples/s does not depend on spp).  Returns
+    (Msamples/s, threads, description, seconds).  `osc`: an OracleScene that already holds the scene."""
     from oracle import binding as B
+    from raytracingoneweekend_b200 import _abi as A
     kind, seed, n_param, W, H, spp, aspect = wl
-    if kind == "many_spheres":
-        n_param = min(n_param, 10000)  # O(N) per segment: the brute-force reference cannot take 1e6
-    fz = api.FrozenHittableList.generate(kind, seed, n_param)
-    osc = oracle_scene_from(fz)
-    cam = make_camera(api, aspect)
+    capped = kind == "many_spheres" and n_param > 10000
+    if capped:
+        n_param = 10000  # O(N) per segment: the brute-force reference cannot take 1e6
+        osc = None
+    if osc is None:
+        osc = oracle_scene_for(kind, seed, n_param)
+    cam = B.camera_new(LOOKFROM.get(kind, (13, 2, 3)), (0, 0, 0), (0, 1, 0), 20.0, aspect, 0.1, 10.0)
     nthreads = threads or max(1, B.lib().omo_hardware_threads() - 1)
     chunks = (W * H + 2729) // 2730
 
     def run(world):
-        p = api.render_params(W, H, 1, MAX_DEPTH, TMIN, TMAX, seed=1, flags=0, part_rank=0, part_world=world)
+        p = A.RenderParams(W, H, 1, MAX_DEPTH, TMIN, TMAX, 1, 0, 0, 0, 0, world, 0)
         t0 = time.perf_counter()
         r = osc.render(cam, p, nthreads=nthreads)
         return r["traced"], time.perf_counter() - t0
@@ -127,39 +173,53 @@ def cpu_reference_rate(api, wl, seconds_target=10.0, threads=0):
         n, dt = run(world2)
         world = world2
     desc = "%s %dx%d, 1 spp over every %d-th 2730-pixel chunk (%d samples), depth %d" % (kind, W, H, world, n, MAX_DEPTH)
-    if kind == "many_spheres":
-        desc += ", N capped at %d spheres" % n_param
+    if capped:
+        desc += ", N capped at %d spheres (the reference scans every object per segment)" % n_param
     return n / dt / 1e6, nthreads, desc, dt
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path (its C++ restatement in
-    oracle/, since the Rust crate cannot be built here) on the box's host cores."""
+    """--impl reference: the reference's CPU implementation of the path (its C++ restatement in oracle/, since the Rust crate
+    cannot be built here) on the box's host cores.  Loads oracle/libom_oracle.so only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from raytracingoneweekend_b200 import api
     wl = WORKLOADS[args.workload]
+    kind, seed, n_param, W, H, spp, aspect = wl
+    osc = None if (kind == "many_spheres" and n_param > 10000) else oracle_scene_for(kind, seed, n_param)
     rates, desc, threads = [], "", 0
     per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     t_all = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        rate, threads, desc, dt = cpu_reference_rate(api, wl, seconds_target=per_step)
+        rate, threads, desc, dt = cpu_reference_rate(wl, seconds_target=per_step, osc=osc)
         if i >= args.warmup:
             rates.append((rate, dt))
     value = float(np.mean([r for r, _ in rates]))
     ms = float(np.mean([dt for _, dt in rates]) * 1e3)
-    kind, seed, n_param, W, H, spp, aspect = wl
     line = {
         "impl": "reference", "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "%s: %s %dx%d, %d spp, depth %d" % (args.workload, kind, W, H, spp, MAX_DEPTH), "sampled": desc},
+        "config": {"workload": "%s: %s %dx%d, %d spp, depth %d" % (args.workload, kind, W, H, spp, MAX_DEPTH), "sampled": desc,
+                   "build": "oracle/Makefile: g++ -O2 -ffp-contract=off (rustc release has no target-cpu=native either)"},
         "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.perf_counter() - t_all,
     }
     _OUT.write(json.dumps(line) + "\n"); _OUT.flush()
+
+
+def pixels_agree(a, b, exact):
+    """merge_check: rank 0's merged frame against a single-GPU render of the same job."""
+    out = {"n_equal": bool((a["n"] == b["n"]).all()), "bloom_equal": bool((a["bloom"] == b["bloom"]).all()),
+           "color_equal_frac": float((a["color"] == b["color"]).all(axis=1).mean())}
+    with np.errstate(invalid="ignore", divide="ignore"):
+        rel = np.abs(a["sum"].astype(np.float64) - b["sum"]) / np.maximum(np.abs(b["sum"]), 1e-3)
+    out["sum_max_rel"] = float(rel.max())
+    out["bit_identical"] = bool(all((np.ascontiguousarray(a[f]).view(np.uint8) == np.ascontiguousarray(b[f]).view(np.uint8)).all()
+                                    for f in ("sum", "n", "avg_depth", "bad_avgs", "bloom", "color")))
+    out["ok"] = out["bit_identical"] if exact else (out["n_equal"] and out["bloom_equal"] and out["color_equal_frac"] >= 0.999 and out["sum_max_rel"] <= 1e-5)
+    return out
 
 
 def run_ours(args):
@@ -182,55 +242,121 @@ def run_ours(args):
     kind, seed, n_param, W, H, spp, aspect = WORKLOADS[args.workload]
     if args.spp:
         spp = args.spp
-    fz = api.FrozenHittableList.generate(kind, seed, n_param)
-    cam = make_camera(api, aspect)
+    freeze_flags = A.FREEZE_GPU_BVH if (kind == "many_spheres" and n_param >= 100000) else 0  # device BVH build above ~1e5 primitives
+    fz = api.FrozenHittableList.generate(kind, seed, n_param, flags=freeze_flags)
+    cam = make_camera(api, aspect, kind)
     kw = dict(max_depth=MAX_DEPTH, tmin=TMIN, tmax=TMAX, seed=1)
     if args.wavefront:
         kw["flags"] = A.RENDER_WAVEFRONT
-    dr = D.DistributedRenderer(fz, cam, W, H, spp, rank, world, mode="spp", device=local, **kw)
+    if args.pool:
+        kw["flags"] = A.RENDER_POOL
     stream = torch.cuda.Stream(device=local)  # a real stream: pointer 0 would mean "the handle's own"
     torch.cuda.set_stream(stream)              # NCCL collectives and the events below use it too
-    dr.r.set_stream(stream.cuda_stream)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step():
-        dr.r.reset()
-        dr.render()
+    # ---- the job ------------------------------------------------------------------------------------------------------
+    phases = {}     # name -> [ms per timed step] (CUDA events on the stream)
+    marks = []      # (name, event) of the current step
+
+    def mark(name):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(stream)
+        marks.append((name, ev))
+
+    def make_job(frozen):
+        if args.adaptive:
+            s = D.AdaptiveScheduler(frozen, cam, W, H, spp, rank, world, pass_spp=args.pass_spp, device=local, rebalance=False, **kw)
+            s.r.set_stream(stream.cuda_stream)
+            return s
+        d = D.DistributedRenderer(frozen, cam, W, H, spp, rank, world, mode="spp", device=local, **kw)
+        d.use_torch_stream(stream)
+        return d
+
+    job = make_job(fz)
+
+    def run_job(j, timed=False):
+        j.r.reset()
+        if args.adaptive:
+            j.credited, j.history = 0, []
+            j.run()
+            return
+        if timed:
+            mark("start")
+        j.render()
+        if timed:
+            mark("render")
         if world > 1:
-            dr.exchange()
+            j.exchange(mark if timed else None)
+
+    def step(timed=False):
+        del marks[:]
+        run_job(job, timed)
+        return list(marks)
 
     for _ in range(args.warmup):
         step()
     barrier()
-    dr.r.elapsed_ms()  # drop warm-up launch timings
-    kernels0 = dr.r.perf_counters()["kernels"]
+    job.r.elapsed_ms()  # drop warm-up launch timings
+    kernels0 = job.r.perf_counters()["kernels"]
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    all_marks = []
     barrier()
     e0.record(stream)
     for _ in range(args.steps):
-        step()
+        all_marks.append(step(timed=True))
     e1.record(stream)
     barrier()
     ms_total = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
+    for ms_ in all_marks:
+        for (_, a), (name, b) in zip(ms_[:-1], ms_[1:]):
+            phases.setdefault(name, []).append(a.elapsed_time(b))
+    phase_ms = {k: float(np.mean(v)) for k, v in phases.items()}
     if world > 1:
-        t = torch.tensor([ms_total], device="cuda")
+        t = torch.tensor([ms_total, phase_ms.get("render", 0.0)], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-    kern_ms, kern_launches = dr.r.elapsed_ms()
-    pcs = dr.r.perf_counters()
+        ms_total, slowest_render = float(t[0].item()), float(t[1].item())
+        phase_ms["render_slowest_rank"] = slowest_render
+    kern_ms, kern_launches = job.r.elapsed_ms()
+    pcs = job.r.perf_counters()
     kernels_timed = pcs["kernels"] - kernels0
     wavefront = bool(pcs["flags"] & A.RENDER_WAVEFRONT)
-    samples_step = W * H * spp
+    pool = bool(pcs["flags"] & A.RENDER_POOL)
+    # samples of one step: fixed spp = every pixel x spp; adaptive = what was actually traced (rank 0 holds the whole frame)
+    merged = job.r.read_pixels().copy() if (rank == 0 and (world > 1 or args.adaptive)) else None
+    samples_step = int(merged["n"].astype(np.int64).sum()) if (rank == 0 and args.adaptive) else W * H * spp
+    if world > 1 and args.adaptive:
+        t = torch.tensor([samples_step], dtype=torch.int64, device="cuda")
+        dist.broadcast(t, src=0)
+        samples_step = int(t.item())
     value = samples_step * args.steps / (ms_total * 1e-3) / 1e6
-    traced = dr.r.samples_traced()
+    traced = job.r.samples_traced()
+
+    # ---- merge_check: the N-GPU frame against one GPU rendering the whole job alone -----------------------------------------
+    merge_check = None
+    if rank == 0 and (world > 1 or args.adaptive):
+        flags1 = kw.get("flags", 0) | (A.RENDER_ADAPTIVE if args.adaptive else 0)
+        r1 = api.Renderer(fz, cam, api.render_params(W, H, spp, flags=flags1, device=local, **{k: v for k, v in kw.items() if k != "flags"}))
+        if args.adaptive:
+            for _ in range((spp + args.pass_spp - 1) // args.pass_spp):
+                r1.launch(args.pass_spp)
+        else:
+            r1.launch(0)
+        r1.sync()
+        alone = r1.read_pixels()
+        r1.close()
+        # adaptive frames are bit-identical by construction (one owner per pixel); spp slices add float partial sums in another order
+        merge_check = pixels_agree(merged, alone, exact=args.adaptive)
+        merge_check["against"] = "one GPU rendering the same job alone (%s)" % ("adaptive, same passes" if args.adaptive else "fixed spp")
+        if not args.adaptive:
+            merge_check["all_pixels_have_spp"] = bool((merged["n"] == spp).all())
 
     # ---- end to end through the public API with host buffers ------------------------------------
     lists = fz.lists()
@@ -244,17 +370,15 @@ def run_ours(args):
         for k, arr in lists.items():
             if len(arr):
                 api._lib.call("om_scene_add_" + k, world_list.h, arr, len(arr))
-        api._lib.call("om_scene_freeze", world_list.h, None, 0)
-        d2 = D.DistributedRenderer(world_list, cam, W, H, spp, rank, world, mode="spp", device=local, **kw)
-        d2.render()
-        if world > 1:
-            d2.exchange()
+        api._lib.call("om_scene_freeze", world_list.h, None, freeze_flags)
+        j2 = make_job(world_list)
+        run_job(j2)
         if rank == 0:
-            d2.r.read_pixels(px)
+            j2.r.read_pixels(px)
         else:
-            d2.r.sync()
+            j2.r.sync()
         h2d = world_list.stats()["device_bytes"] + spp
-        d2.close()
+        j2.close()
 
     e2e_step()
     barrier()
@@ -271,46 +395,78 @@ def run_ours(args):
 
     line = None
     if rank == 0:
-        # ---- roofline of the dominant kernel (k_render): executed work x SURVEY §8(d) constants ----
+        # ---- roofline of the dominant kernel: executed work x SURVEY §8(d) constants ----
         kwc = dict(kw); kwc["flags"] = kw.get("flags", 0) | A.RENDER_COUNTERS
-        pc = api.render_params(W, H, 16, device=local, **kwc)
-        rc = api.Renderer(fz, cam, pc)
+        spp_c = min(spp, 16)
+        rc = api.Renderer(fz, cam, api.render_params(W, H, spp_c, device=local, **kwc))
         rc.launch(0)
         rc.sync()
         c = rc.perf_counters()
         rc.close()
-        fps = flops_per_sample(c, c["traced"])
-        peak_tf, _ = api.fp32_peak(local)
+        per_sample = {k: c[k] / c["traced"] for k in ("segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals")}
+        in_smem = bool(pcs["scene_in_smem"])
+        ncu = load_ncu(args.workload + ("_pool" if pool else ""))
+        kernel = ("k_wf_extend + k_wf_shade + k_wf_compact (+ k_render tail)" if wavefront else ("k_render_pool" if pool else "k_render"))
         launch_ms = kern_ms / max(1, kern_launches)
-        samples_launch = W * H * (D.spp_slices(spp, world)[0][1])
-        achieved_tf = fps * samples_launch / (launch_ms * 1e-3) / 1e12
-        roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf, "traffic": NCU_DRAM_BYTES.get((args.workload, spp, world, wavefront)),
-                    "traffic_source": "profiles/r1_v1e_c2_1024spp_dram.csv: ncu dram__bytes_read.sum + dram__bytes_write.sum of this launch (122 MB read + 558 MB written: the 2 x 66 MB "
-                                      "framebuffer pass plus write-backs of the traversal stack); the full section set was captured at 16 spp (profiles/r1_v1g_c2_k_render.txt)" if (args.workload, spp, world, wavefront) in NCU_DRAM_BYTES else None,
-                    "peak_source": "FMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
-                    "flops_per_sample": fps, "kernel": "k_wf_extend + k_wf_shade + k_wf_compact (+ k_render tail)" if wavefront else "k_render", "launch_ms": launch_ms,
-                    "per_sample": {k: c[k] / c["traced"] for k in ("segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals")},
-                    "accumulate_hbm": {"bytes_per_launch": 64 * W * H, "note": "32 B read + 32 B write per pixel per launch"},
-                    "ncu": NCU_K_RENDER_C2 if (args.workload == "C2" and not wavefront) else None}
+        samples_launch = samples_step / max(1, kern_launches // max(1, args.steps)) if args.adaptive else W * H * (D.spp_slices(spp, world)[0][1])
+        traffic = None
+        if ncu and ncu.get("dram_bytes") and ncu["dram_bytes"].get("spp") == (spp if world == 1 else -1):
+            traffic = ncu["dram_bytes"]["read"] + ncu["dram_bytes"]["write"]
+        if in_smem:  # C1-C4: the scene lives in shared memory, the path is FP32 / issue bound
+            fps = flops_per_sample(c, c["traced"])
+            peak_tf, _ = api.fp32_peak(local)
+            achieved = fps * samples_launch / (launch_ms * 1e-3) / 1e12
+            roofline = {"bound": "fp32", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                        "peak_source": "FMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)", "flops_per_sample": fps}
+        else:        # C5: nodes and primitives are fetched through L2 / HBM: bytes against the measured HBM peak
+            bps = bytes_per_sample(c, c["traced"], spp)
+            peaks = {}
+            try:
+                peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            except (OSError, ValueError):
+                pass
+            peak_gbs = float(peaks.get("hbm_gbs", 6550.4))
+            achieved = bps * samples_step / (ms_total / args.steps * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+                        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6550.4",
+                        "bytes_per_sample": bps, "note": "bytes the traversal asks for (112 B per node visit, 48 B per sphere test, 80 B per hit, 64 B framebuffer per pixel); "
+                                                         "the 180 MB scene image is mostly served by the 126 MB L2, so DRAM traffic is lower than this"}
+        roofline.update({"traffic": traffic, "traffic_source": (ncu or {}).get("dram_bytes", {}).get("source") if traffic else None, "kernel": kernel,
+                         "launch_ms": launch_ms, "per_sample": per_sample,
+                         "accumulate_hbm": {"bytes_per_launch": 64 * W * H, "note": "32 B read + 32 B write per pixel per launch"},
+                         "ncu": {k: v for k, v in (ncu or {}).items() if k != "dram_bytes"} or None})
         cpu = None
         if world == 1 and not args.no_cpu:
-            rate, threads, desc, _ = cpu_reference_rate(api, WORKLOADS[args.workload], seconds_target=12.0)
+            from oracle import binding as B
+            osc = None
+            if not (kind == "many_spheres" and n_param > 10000):
+                osc = B.OracleScene()
+                for k, arr in lists.items():
+                    osc.add(k, arr)
+            rate, threads, desc, _ = cpu_reference_rate(WORKLOADS[args.workload], seconds_target=12.0, osc=osc)
             cpu = {"value": rate, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": desc}
+        mode = "adaptive (bad_avgs >= 5 retires a pixel), max %d spp, passes of %d" % (spp, args.pass_spp) if args.adaptive else "fixed spp"
         line = {
             "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": "%s: %s %dx%d, %d spp, depth %d, fixed spp" % (args.workload, kind, W, H, spp, MAX_DEPTH),
-                       "partition": "spp slices + 1 NCCL reduce" if world > 1 else "single GPU", "pipeline": ("wavefront" if wavefront else "persistent kernel") + ("" if args.wavefront else " (library's choice)"),
+            "config": {"workload": "%s: %s %dx%d, %d spp, depth %d, %s" % (args.workload, kind, W, H, spp, MAX_DEPTH, mode),
+                       "partition": ("interleaved 2730-pixel chunks + 1 all-reduce of the pixel states per pass" if args.adaptive else "spp slices + 1 NCCL reduce") if world > 1 else "single GPU",
+                       "pipeline": ("wavefront" if wavefront else ("path pool" if pool else "persistent kernel")) + ("" if (args.wavefront or args.pool) else " (library's choice)"),
                        "l2": "scene image %.1f MB %s; per-step traffic beyond it is the %d MB framebuffer, rewritten by reset() every step"
-                             % (fz.stats()["device_bytes"] / 1e6, "with its hot part in shared memory" if pcs["scene_in_smem"] else "read through L1/L2 (larger than shared memory)", W * H * 32 // 1000000)},
+                             % (fz.stats()["device_bytes"] / 1e6, "with its hot part in shared memory" if in_smem else "read through L1/L2 (larger than shared memory)", W * H * 32 // 1000000),
+                       "tile_order": "the timed steps reuse the tile-cost order that the first warm-up step measured with a pilot launch of 1/64 of the samples; the e2e figure creates a fresh handle per step and pays for the pilot every time"},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 40},
-            "gpu_launches": int(kernels_timed) + args.steps * (3 if world > 1 else 0),
-            "clocks": clocks, "roofline": roofline, "samples_traced_rank0": traced,
+            "gpu_launches": int(kernels_timed) + args.steps * (3 if (world > 1 and not args.adaptive) else 0),
+            "clocks": clocks, "roofline": roofline, "samples_traced_rank0": traced, "samples_per_step": samples_step,
         }
+        if phase_ms:
+            line["phase_ms"] = phase_ms  # CUDA events on rank 0's stream, mean over the timed steps; render_slowest_rank = max over ranks
+        if merge_check:
+            line["merge_check"] = merge_check
         if cpu:
             line["cpu_baseline"] = cpu
-    dr.close()
+    job.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -327,7 +483,10 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (a smaller number is NOT the headline config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--wavefront", action="store_true", help="use the wavefront pipeline (OM_RENDER_WAVEFRONT) instead of the persistent kernel")
+    ap.add_argument("--wavefront", action="store_true", help="use the global wavefront pipeline (OM_RENDER_WAVEFRONT) instead of the library's choice")
+    ap.add_argument("--pool", action="store_true", help="use the CTA-resident wavefront (OM_RENDER_POOL)")
+    ap.add_argument("--adaptive", action="store_true", help="the reference's adaptive mode (OM_RENDER_ADAPTIVE) through dist.AdaptiveScheduler; value counts the samples actually traced")
+    ap.add_argument("--pass-spp", type=int, default=16, help="--adaptive: samples per pass between retirement checks / exchanges")
     args = ap.parse_args()
     # ONE JSON line on stdout: native libraries print there too (NCCL's version banner under NCCL_DEBUG), so file
     # descriptor 1 is pointed at stderr for the run and the line goes to a private copy of the real stdout.

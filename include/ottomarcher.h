@@ -408,6 +408,10 @@ OM_API om_status om_render_live_per_chunk(om_render* r, uint32_t* host_counts, s
 /* dst[i] |= src[k][i] for k < nsrc: the bitwise-OR NCCL does not have. Device pointers.       */
 OM_API om_status om_bloom_or(uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc, size_t n,
                              int32_t device);
+/* The same OR over width*height masks on the HANDLE'S stream, without synchronising: ordered like every other call on the
+ * handle (om_bloom_or runs on the legacy default stream and synchronises the device, which does not order it against a
+ * non-blocking stream that a collective was issued on).                                                                */
+OM_API om_status om_render_bloom_or(om_render* r, uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc);
 
 /* Parity hook: closest hit of arbitrary rays against a frozen scene, on the device, with the
  * semantics of FrozenHittableList::hit (hits.rs:270-334).  dirs are normalised first like

@@ -60,6 +60,7 @@ PROTOTYPES = {
     "om_render_export_accum": ("st", [vp, vp, vp]),
     "om_render_import_accum": ("st", [vp, vp, vp]),
     "om_bloom_or": ("st", [vp, vp, sz, sz, i32]),
+    "om_render_bloom_or": ("st", [vp, vp, vp, sz]),
     "om_render_set_chunk_owners": ("st", [vp, vp, sz, u32]),
     "om_render_export_state": ("st", [vp, vp, u32]),
     "om_render_import_state": ("st", [vp, vp]),

@@ -393,6 +393,10 @@ class Renderer:
     def export_accum(self, dev_acc_ptr, dev_bloom_ptr):
         _lib.call("om_render_export_accum", self.h, dev_acc_ptr, dev_bloom_ptr)
 
+    def bloom_or(self, dev_dst_ptr, dev_src_ptr, nsrc):
+        """dst[i] |= src[k][i] for k < nsrc over the frame's masks, on the handle's stream (no synchronisation)."""
+        _lib.call("om_render_bloom_or", self.h, dev_dst_ptr, dev_src_ptr, nsrc)
+
     def import_accum(self, dev_acc_ptr, dev_bloom_ptr):
         _lib.call("om_render_import_accum", self.h, dev_acc_ptr, dev_bloom_ptr)
 

@@ -975,6 +975,14 @@ om_status om_bloom_or(uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc, s
     return OM_OK;
 }
 
+om_status om_render_bloom_or(om_render* r, uint64_t* dev_dst, const uint64_t* dev_src, size_t nsrc) {
+    if (!r || !dev_dst || (!dev_src && nsrc)) return fail(OM_ERR_INVALID, "om_render_bloom_or: NULL argument");
+    CU(cudaSetDevice(r->dev));
+    k_bloom_or<<<ublocks(r->npx), UT, 0, r->stream>>>((unsigned long long*)dev_dst, (const unsigned long long*)dev_src, (uint32_t)nsrc, (size_t)r->npx);
+    CU(cudaGetLastError());
+    return OM_OK;
+}
+
 om_status om_trace_rays(const om_scene* frozen, const float* origins, const float* dirs, size_t n, float tmin, float tmax, uint32_t flags, int32_t device,
                         uint64_t* ids, float* t, float* points, float* normals) {
     if (!frozen || !frozen->frozen) return fail(OM_ERR_INVALID, "om_trace_rays: scene is not frozen");

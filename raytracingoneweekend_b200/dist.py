@@ -52,9 +52,12 @@ def merge_accum(acc_list, bloom_list):
     return acc, bloom
 
 
-def reduce_to_rank0(acc_t, bloom_t, group=None):
+def reduce_to_rank0(acc_t, bloom_t, group=None, gather_buf=None, mark=None, renderer=None):
     """acc_t: float32 tensor [npx,8]; bloom_t: int64 tensor [npx], both on this rank's device.
-    After the call rank 0 holds the merged values in place.  One reduce + one gather."""
+    After the call rank 0 holds the merged values in place.  One reduce + one gather.
+    gather_buf: rank 0's [world, npx] int64 landing buffer (the gather writes its rows directly; allocated here if None).
+    mark(name): optional callback after each step (per-phase timing).
+    renderer: an api.Renderer whose stream is torch's current stream; the OR then runs there (om_render_bloom_or)."""
     import torch
     import torch.distributed as dist
 
@@ -63,18 +66,28 @@ def reduce_to_rank0(acc_t, bloom_t, group=None):
     if world == 1:
         return acc_t, bloom_t
     dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM, group=group)
-    gathered = [torch.empty_like(bloom_t) for _ in range(world)] if rank == 0 else None
-    dist.gather(bloom_t, gather_list=gathered, dst=0, group=group)
+    if mark:
+        mark("reduce")
+    rows = None
     if rank == 0:
-        stacked = torch.stack(gathered, 0)
-        if stacked.is_cuda:
+        if gather_buf is None:
+            gather_buf = torch.empty((world, bloom_t.numel()), dtype=bloom_t.dtype, device=bloom_t.device)
+        rows = [gather_buf[k] for k in range(world)]  # views of one buffer: the ranks' rows land side by side, no stacking copy
+    dist.gather(bloom_t, gather_list=rows, dst=0, group=group)
+    if rank == 0:
+        if gather_buf.is_cuda and renderer is not None:
+            renderer.bloom_or(bloom_t.data_ptr(), gather_buf.data_ptr(), world)  # on the handle's stream, in order with the gather
+        elif gather_buf.is_cuda:
             from . import _lib
-            _lib.call("om_bloom_or", bloom_t.data_ptr(), stacked.data_ptr(), world, bloom_t.numel(), bloom_t.device.index)
+            torch.cuda.synchronize(bloom_t.device)  # om_bloom_or runs on the legacy stream: the gather must have landed first
+            _lib.call("om_bloom_or", bloom_t.data_ptr(), gather_buf.data_ptr(), world, bloom_t.numel(), bloom_t.device.index)
         else:
-            out = stacked[0].clone()
+            out = gather_buf[0].clone()
             for k in range(1, world):
-                out |= stacked[k]
+                out |= gather_buf[k]
             bloom_t.copy_(out)
+    if mark:
+        mark("gather_or")
     return acc_t, bloom_t
 
 
@@ -102,17 +115,33 @@ class DistributedRenderer:
         dev = torch.device("cuda", self.device)
         self.acc = torch.empty((npx, 8), dtype=torch.float32, device=dev)
         self.bloom = torch.empty((npx,), dtype=torch.int64, device=dev)
+        self.gather_buf = torch.empty((world, npx), dtype=torch.int64, device=dev) if (rank == 0 and world > 1) else None
+        self.shares_torch_stream = False
+
+    def use_torch_stream(self, stream):
+        """Run the handle's kernels on `stream` (a torch.cuda.Stream that is also torch's current stream): the collectives are
+        ordered against it by torch, so exchange() needs no device-wide synchronize between the collective and the import."""
+        self.r.set_stream(stream.cuda_stream)
+        self.shares_torch_stream = True
 
     def render(self):
         self.r.launch(0)
 
-    def exchange(self):
-        """export -> collective -> import on rank 0.  Returns after rank 0 holds the full image."""
+    def exchange(self, mark=None):
+        """export -> collective -> import on rank 0.  Rank 0 holds the full image once its stream has run the import.
+        mark(name) is called after each phase (export, reduce, gather_or, import) for per-phase timing."""
         self.r.export_accum(self.acc.data_ptr(), self.bloom.data_ptr())
-        reduce_to_rank0(self.acc, self.bloom)
+        if mark:
+            mark("export")
+        if not self.shares_torch_stream and self.world > 1:
+            self.r.sync()  # the export ran on the handle's own stream, which torch knows nothing about
+        reduce_to_rank0(self.acc, self.bloom, gather_buf=self.gather_buf, mark=mark, renderer=self.r if self.shares_torch_stream else None)
         if self.rank == 0 and self.world > 1:
-            self.torch.cuda.synchronize(self.device)
+            if not self.shares_torch_stream:
+                self.torch.cuda.synchronize(self.device)
             self.r.import_accum(self.acc.data_ptr(), self.bloom.data_ptr())
+        if mark:
+            mark("import")
 
     def close(self):
         self.r.close()

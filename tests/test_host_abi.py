@@ -169,3 +169,16 @@ def test_host_bvh_depth_stays_below_the_traversal_stack(api, A):
         w += api.Sphere.new_with_radius((2.0 ** k, 0.0, 0.0), 0.1 * 2.0 ** k, m)
     st = w.freeze(flags=A.FREEZE_NO_ALWAYS_LIST).stats()
     assert st["bvh_prims"] == 201 and st["bvh_depth"] <= 62
+
+
+def test_reference_arm_never_loads_the_product_library():
+    """bench.py --impl reference builds its scene with the oracle alone: after timing a sample of C1 the process
+    maps oracle/libom_oracle.so and not libottomarcher_cuda.so."""
+    import subprocess, sys
+    code = ("import sys; sys.path.insert(0, %r); import bench\n"
+            "rate, threads, desc, dt = bench.cpu_reference_rate(bench.WORKLOADS['C1'], seconds_target=0.5, threads=2)\n"
+            "maps = open('/proc/self/maps').read()\n"
+            "assert rate > 0 and 'libom_oracle.so' in maps and 'libottomarcher_cuda' not in maps, maps\n"
+            "print('ok', desc)\n") % ROOT
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and out.stdout.startswith("ok"), out.stderr[-2000:]
