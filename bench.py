@@ -218,7 +218,12 @@ def pixels_agree(a, b, exact):
     out["sum_max_rel"] = float(rel.max())
     out["bit_identical"] = bool(all((np.ascontiguousarray(a[f]).view(np.uint8) == np.ascontiguousarray(b[f]).view(np.uint8)).all()
                                     for f in ("sum", "n", "avg_depth", "bad_avgs", "bloom", "color")))
-    out["ok"] = out["bit_identical"] if exact else (out["n_equal"] and out["bloom_equal"] and out["color_equal_frac"] >= 0.999 and out["sum_max_rel"] <= 1e-5)
+    # spp slices add a pixel's samples as N partial sums instead of one running sum: two orders of the same n f32 terms differ by
+    # at most ~n * 2^-24 relative to the sum of their magnitudes (1024 spp: 6.1e-5); the 8-bit colour may flip where sqrt(sum/n)*256
+    # sits on an integer
+    n_max = int(b["n"].max()) if b["n"].size else 1
+    out["sum_rel_bound"] = max(1e-5, n_max * 2.0 ** -24)
+    out["ok"] = out["bit_identical"] if exact else (out["n_equal"] and out["bloom_equal"] and out["color_equal_frac"] >= 0.999 and out["sum_max_rel"] <= out["sum_rel_bound"])
     return out
 
 

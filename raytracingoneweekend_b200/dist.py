@@ -10,6 +10,8 @@ and ONE exchange at the end brings the accumulators to rank 0: a SUM reduce of
 {sum.rgb, n, n*avg_depth, bad_avgs} and a gather + bitwise OR of the 64-bit bloom masks (NCCL has
 no OR).  The merge arithmetic is plain tensor code so the gloo/CPU tests exercise the same path.
 """
+import os
+
 import numpy as np
 
 from . import _abi as A
@@ -65,7 +67,10 @@ def reduce_to_rank0(acc_t, bloom_t, group=None, gather_buf=None, mark=None, rend
     rank = dist.get_rank(group)
     if world == 1:
         return acc_t, bloom_t
-    dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM, group=group)
+    if os.environ.get("OM_DIST_ALLREDUCE"):  # A/B switch: an all-reduce can ride NVSwitch's in-switch reduction where a rooted reduce is a tree
+        dist.all_reduce(acc_t, op=dist.ReduceOp.SUM, group=group)
+    else:
+        dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM, group=group)
     if mark:
         mark("reduce")
     rows = None

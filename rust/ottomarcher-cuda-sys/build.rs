@@ -10,8 +10,9 @@ fn main() {
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "nvcc".into());
     let common = ["-O3", "-std=c++17", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
                   "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-fvisibility=hidden"];
-    let sources: [(&str, &[&str]); 6] = [
-        ("om_kernels_fast.cu", &[]), ("om_kernels_exact.cu", &["-fmad=false"]), ("om_api.cu", &["-fmad=false"]),
+    // the same list and per-file flags as raytracingoneweekend_b200/build.py SOURCES (tests/test_rust_ffi.py compares the two)
+    let sources: [(&str, &[&str]); 7] = [
+        ("om_kernels_fast.cu", &[]), ("om_kernels_exact.cu", &["-fmad=false"]), ("om_api.cu", &["-fmad=false"]), ("om_lbvh.cu", &[]),
         ("om_host.cpp", &[]), ("om_scene.cpp", &[]), ("om_bvh.cpp", &[]),
     ];
     let mut objs = Vec::new();

@@ -1,131 +1,31 @@
-//! FFI mirror of include/ottomarcher.h (B200 / sm_100a renderer for ottomarcher).
-//! NOT COMPILED IN THIS IMAGE (no rustc/cargo): written to the header, checked by eye and by the
-//! ctypes mirror's sizeof/offset tests (tests/test_host_abi.py), which bind the same structs.
+//! FFI binding of include/ottomarcher.h (B200 / sm_100a renderer for ottomarcher) and the safe wrapper that replaces
+//! main.rs:196-214.
+//! NOT COMPILED IN THIS IMAGE (no rustc/cargo).  What keeps it honest instead:
+//!  * `ffi.rs` (constants, #[repr(C)] structs, the extern "C" block) is GENERATED from the header by tools/gen_rust_ffi.py;
+//!  * tests/test_rust_ffi.py fails when it is stale, when a symbol / argument count differs from the header or from the
+//!    built library's exports, and when a struct's size or a field's offset differs from the ctypes mirrors that every GPU
+//!    test binds (raytracingoneweekend_b200/_abi.py).
 #![allow(non_camel_case_types, non_upper_case_globals, dead_code)]
-use std::os::raw::{c_char, c_void};
+mod ffi;
+pub use ffi::*;
+/// `From<&Sphere> for om_sphere` and friends, written against the reference's own types; compiled inside the ottomarcher crate
+/// (`--features ottomarcher`), where those types live.
+#[cfg(feature = "ottomarcher")]
+pub mod convert;
 
-pub type om_status = u32;
-pub const OM_OK: om_status = 0;
-pub const OM_ERR_INVALID: om_status = 1;
-pub const OM_ERR_CUDA: om_status = 2;
-pub const OM_ERR_UNSUPPORTED: om_status = 3;
-pub const OM_ERR_OOM: om_status = 4;
-pub const OM_ERR_NO_DEVICE: om_status = 5;
-
-pub const OM_RENDER_ADAPTIVE: u32 = 1 << 0;
-pub const OM_RENDER_FAST_MATH: u32 = 1 << 1;
-pub const OM_RENDER_BRUTE_FORCE: u32 = 1 << 2;
-pub const OM_RENDER_NO_SMEM_SCENE: u32 = 1 << 4;
-pub const OM_RENDER_COUNTERS: u32 = 1 << 5;
-pub const OM_RENDER_WAVEFRONT: u32 = 1 << 3;
-pub const OM_RENDER_PERSISTENT: u32 = 1 << 6;
-pub const OM_RENDER_PHASE_ALIGN: u32 = 1 << 7;
-pub const OM_RENDER_NO_PHASE_ALIGN: u32 = 1 << 8;
-pub const OM_FREEZE_NO_ALWAYS_LIST: u32 = 1 << 0;
-pub const OM_FREEZE_RAY_PADDING: u32 = 1 << 1;
-pub const OM_FREEZE_STATIC_PADDING: u32 = 1 << 2;
-pub const OM_FREEZE_NO_MARCHED_BVH: u32 = 1 << 3;
-pub const OM_FREEZE_GPU_BVH: u32 = 1 << 4;
-
-/// materials.rs:11-23
-#[repr(C)] #[derive(Clone, Copy, Default)]
-pub struct om_material { pub albedo: [f32; 3], pub fuzz: f32, pub ior: f32, pub mat_type: u32 }
-/// traced.rs:13-19 / 229-235 (Sphere and Cube share the layout)
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_sphere { pub m_local_to_world: [f32; 16], pub m_world_to_local: [f32; 16], pub material: om_material }
-pub type om_cube = om_sphere;
-/// traced.rs:77-82
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_infinite_plane { pub center: [f32; 3], pub normal: [f32; 3], pub material: om_material }
-/// traced.rs:118-131
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_barycentric {
-    pub origin: [f32; 3], pub u: [f32; 3], pub u_length: f32, pub v: [f32; 3], pub v_length: f32,
-    pub uxv: [f32; 3], pub uxvxu: [f32; 3], pub base_inv: [f32; 9], pub v_in_base: [f32; 3], pub material: om_material,
+impl Default for om_pixel {
+    fn default() -> Self { om_pixel { sum: [0.0; 3], n: 0, avg_depth: 0.0, bad_avgs: 0, bloom: 0, color: [0; 3], _pad: [0; 5] } }
 }
-/// marched.rs:49-54, 78-83, 104-113
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_marched_sphere { pub center: [f32; 3], pub radius: f32, pub material: om_material }
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_marched_box { pub center: [f32; 3], pub sizes: [f32; 3], pub material: om_material }
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_marched_torus {
-    pub m_local_to_world_translate_rotate: [f32; 16], pub m_world_to_local_translate_rotate: [f32; 16],
-    pub m_local_to_world_scale: [f32; 4], pub m_world_to_local_scale: [f32; 4], pub sizes: [f32; 3], pub material: om_material,
+impl Default for om_render_params {
+    fn default() -> Self {
+        om_render_params { width: 0, height: 0, spp_max: 0, max_depth: 50, tmin: 0.001, tmax: 100.0, seed: 0, flags: 0, sample_base: 0, sample_count: 0,
+                           part_rank: 0, part_world: 1, device: -1 }
+    }
 }
-/// `Arc<dyn Marched + Send + Sync>` as data (marched.rs:8-45): to_local / to_world matrices, to_world_f factor, world bounds
-/// (or +-INF); local_sdf travels beside it as a postfix f32 program (OM_SDF_* opcodes, see ottomarcher.h).
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_dyn_marched {
-    pub m_world_to_local: [f32; 16], pub m_local_to_world: [f32; 16], pub world_f: f32,
-    pub bounds_lo: [f32; 3], pub bounds_hi: [f32; 3], pub material: om_material,
-}
-pub const OM_SDF_X: u32 = 1; pub const OM_SDF_Y: u32 = 2; pub const OM_SDF_Z: u32 = 3; pub const OM_SDF_CONST: u32 = 4;
-pub const OM_SDF_ADD: u32 = 5; pub const OM_SDF_SUB: u32 = 6; pub const OM_SDF_MUL: u32 = 7; pub const OM_SDF_DIV: u32 = 8;
-pub const OM_SDF_MIN: u32 = 9; pub const OM_SDF_MAX: u32 = 10; pub const OM_SDF_NEG: u32 = 11; pub const OM_SDF_ABS: u32 = 12;
-pub const OM_SDF_SQRT: u32 = 13; pub const OM_SDF_LEN2: u32 = 14; pub const OM_SDF_LEN3: u32 = 15;
-pub const OM_SDF_STORE: u32 = 16; pub const OM_SDF_LOAD: u32 = 17;
-pub const fn om_sdf_insn(op: u32, arg: u32) -> u32 { op | (arg << 8) }
-/// A user type opts in by describing itself as data; `impl DeviceMarched for MyShape` next to `impl Marched for MyShape`.
+/// A user type opts in to the device by describing itself as data: `impl DeviceMarched for MyShape` next to `impl Marched for MyShape`
+/// (marched_objects: Vec<Arc<dyn Marched + Send + Sync>>, hits.rs:40).
 pub trait DeviceMarched {
     fn describe(&self) -> (om_dyn_marched, Vec<u32>);
-}
-/// camera.rs:9-29
-#[repr(C)] #[derive(Clone, Copy)]
-pub struct om_camera {
-    pub origin: [f32; 3], pub horizontal: [f32; 3], pub vertical: [f32; 3], pub lower_left_corner: [f32; 3],
-    pub u_of_plane: [f32; 3], pub v_of_plane: [f32; 3], pub w_of_plane: [f32; 3],
-    pub lens_radius: f32, pub aspect_ratio: f32, pub focus_dist: f32, pub viewport_width: f32, pub viewport_height: f32,
-}
-/// render_thread.rs:9-17 (Stats), 40 bytes
-#[repr(C)] #[derive(Clone, Copy, Default)]
-pub struct om_pixel { pub sum: [f32; 3], pub n: u32, pub avg_depth: f32, pub bad_avgs: u32, pub bloom: u64, pub color: [u8; 3], pub _pad: [u8; 5] }
-#[repr(C)] #[derive(Clone, Copy, Default)]
-pub struct om_render_params {
-    pub width: u32, pub height: u32, pub spp_max: u32, pub max_depth: u32, pub tmin: f32, pub tmax: f32, pub seed: u64,
-    pub flags: u32, pub sample_base: u32, pub sample_count: u32, pub part_rank: u32, pub part_world: u32, pub device: i32,
-}
-#[repr(C)] pub struct om_scene { _p: [u8; 0] }
-#[repr(C)] pub struct om_render { _p: [u8; 0] }
-
-extern "C" {
-    pub fn om_scene_create(out: *mut *mut om_scene) -> om_status;
-    pub fn om_scene_clear(s: *mut om_scene) -> om_status;
-    pub fn om_scene_destroy(s: *mut om_scene) -> om_status;
-    pub fn om_scene_add_spheres(s: *mut om_scene, a: *const om_sphere, n: usize) -> om_status;
-    pub fn om_scene_add_cubes(s: *mut om_scene, a: *const om_cube, n: usize) -> om_status;
-    pub fn om_scene_add_triangles(s: *mut om_scene, a: *const om_barycentric, n: usize) -> om_status;
-    pub fn om_scene_add_infinite_planes(s: *mut om_scene, a: *const om_infinite_plane, n: usize) -> om_status;
-    pub fn om_scene_add_parallelograms(s: *mut om_scene, a: *const om_barycentric, n: usize) -> om_status;
-    pub fn om_scene_add_marched_spheres(s: *mut om_scene, a: *const om_marched_sphere, n: usize) -> om_status;
-    pub fn om_scene_add_marched_boxes(s: *mut om_scene, a: *const om_marched_box, n: usize) -> om_status;
-    pub fn om_scene_add_marched_tori(s: *mut om_scene, a: *const om_marched_torus, n: usize) -> om_status;
-    pub fn om_scene_add_dyn_marched(s: *mut om_scene, obj: *const om_dyn_marched, code: *const u32, n_words: usize) -> om_status;
-    pub fn om_scene_dyn_marched_count(s: *const om_scene, count: *mut u64) -> om_status;
-    pub fn om_scene_get_dyn_marched(s: *const om_scene, index: u64, obj: *mut om_dyn_marched, code: *mut u32, n_words: *mut usize) -> om_status;
-    pub fn om_scene_add_dyn_object(s: *mut om_scene, trait_object: *const c_void) -> om_status;
-    pub fn om_trim_device_cache() -> om_status;
-    pub fn om_scene_freeze(s: *mut om_scene, cam: *const om_camera, flags: u32) -> om_status;
-    pub fn om_render_create(out: *mut *mut om_render, frozen: *const om_scene, cam: *const om_camera, p: *const om_render_params) -> om_status;
-    pub fn om_render_destroy(r: *mut om_render) -> om_status;
-    pub fn om_render_set_stream(r: *mut om_render, cuda_stream: *mut c_void) -> om_status;
-    pub fn om_render_launch(r: *mut om_render, spp_this_pass: u32) -> om_status;
-    pub fn om_render_sync(r: *mut om_render) -> om_status;
-    pub fn om_render_samples_done(r: *mut om_render, credited: *mut u64) -> om_status;
-    pub fn om_render_samples_traced(r: *mut om_render, traced: *mut u64) -> om_status;
-    pub fn om_render_read_pixels(r: *mut om_render, host: *mut om_pixel, n: usize) -> om_status;
-    pub fn om_render_read_rgb(r: *mut om_render, host_rgb: *mut u8, nbytes: usize) -> om_status;
-    pub fn om_render_read_view(r: *mut om_render, mode: u32, host_rgb: *mut u8, nbytes: usize) -> om_status;
-    /// no counterpart in the reference; fixed device scratch, at most OM_VIEW_NOALLOC_MAX_PIXELS (2 097 152) pixels
-    pub fn om_render_read_view_noalloc(r: *mut om_render, mode: u32, host_rgb: *mut u8, nbytes: usize) -> om_status;
-    pub fn om_write_bmp(path: *const c_char, rgb: *const u8, width: u32, height: u32) -> om_status;
-    pub fn om_render_reset(r: *mut om_render) -> om_status;
-    pub fn om_render_primary(r: *mut om_render, mode: u32, sample_index: u32, ids: *mut u64, t: *mut f32, n: usize) -> om_status;
-    pub fn om_render_set_chunk_owners(r: *mut om_render, owners: *const u8, n_chunks: usize, my_id: u32) -> om_status;
-    pub fn om_render_export_state(r: *mut om_render, dev_state: *mut u32, only_owned: u32) -> om_status;
-    pub fn om_render_import_state(r: *mut om_render, dev_state: *const u32) -> om_status;
-    pub fn om_render_live_per_chunk(r: *mut om_render, host_counts: *mut u32, n_chunks: usize) -> om_status;
-    pub fn om_last_error() -> *const c_char;
 }
 
 /// Error text of the last failing call on this thread.
