@@ -145,6 +145,28 @@ typedef struct om_dyn_marched {
     om_material material;
 } om_dyn_marched;
 
+/* `Arc<dyn Traced + Send + Sync>` as data (traced_objects, hits.rs:39,91-95; trait traced.rs:33-35).  Compiled host code cannot
+ * run on the device, so a user type that wants to be traced there describes itself as a QUADRIC SURFACE in its own frame,
+ *     q(p) = A x^2 + B y^2 + C z^2 + D xy + E xz + F yz + G x + H y + I z + J = 0,   q[10] = {A .. J},
+ * optionally cut by an axis-aligned box in that frame (clip_lo / clip_hi, +-INF = uncut): ellipsoids, cylinders, cones,
+ * paraboloids, hyperboloids, and slabs or caps of them.  hit(r, t_min, t_max) is defined like the reference's own Sphere::hit
+ * (traced.rs:38-63), which it reproduces bit for bit for q = {1,1,1,0,0,0,0,0,0,-1}: the ray goes to the local frame without
+ * being renormalised (ray.rs:17-19), a = q2(d), half_b = o.Q.d + (G,H,I).d / 2, c = q(o), the roots (-half_b -+ sqrt(half_b^2 -
+ * a c)) / a are tried nearer first and the first one inside [t_min, t_max] AND inside the clip box is the hit (a == 0: the one
+ * root -c / (2 half_b)); point = M . p_local; normal = unit(M . grad q(p_local) / 2) - the local gradient carried by the
+ * local->world matrix as Sphere and Cube do (traced.rs:59,296), not its inverse transpose.  Objects are scanned after the
+ * parallelograms, as hits.rs:280-285 scans traced_objects after the typed lists (later object wins on equal t).
+ * bounds_lo / bounds_hi: the world box `Bounded::build_world_bounding_box` returns (bounding_box.rs:69-73); +-INF = the trait's
+ * default "draw always" (the object is then tested against every ray).  Object id = OM_OBJ_ID(OM_TYPE_DYN_TRACED, index).     */
+typedef struct om_dyn_traced {
+    float m_local_to_world[16];
+    float m_world_to_local[16];
+    float q[10];
+    float clip_lo[3], clip_hi[3];
+    float bounds_lo[3], bounds_hi[3];
+    om_material material;
+} om_dyn_traced;
+
 /* camera.rs:9-29 Camera (all fields, same order)                                             */
 typedef struct om_camera {
     float origin[3];
@@ -178,7 +200,7 @@ typedef struct om_pixel {
 enum {
     OM_TYPE_SPHERE = 1, OM_TYPE_CUBE = 2, OM_TYPE_TRIANGLE = 3, OM_TYPE_INFINITE_PLANE = 4,
     OM_TYPE_PARALLELOGRAM = 5, OM_TYPE_MARCHED_SPHERE = 6, OM_TYPE_MARCHED_BOX = 7,
-    OM_TYPE_MARCHED_TORUS = 8, OM_TYPE_DYN_MARCHED = 9
+    OM_TYPE_MARCHED_TORUS = 8, OM_TYPE_DYN_MARCHED = 9, OM_TYPE_DYN_TRACED = 10
 };
 #define OM_OBJ_ID(type, index) ((((uint64_t)(type)) << 32) | ((uint64_t)(index) + 1u))
 
@@ -281,13 +303,17 @@ OM_API om_status om_scene_add_dyn_marched(om_scene* s, const om_dyn_marched* obj
  * for *n_words only; on entry *n_words is the capacity of code).                                         */
 OM_API om_status om_scene_dyn_marched_count(const om_scene* s, uint64_t* count);
 OM_API om_status om_scene_get_dyn_marched(const om_scene* s, uint64_t index, om_dyn_marched* obj, uint32_t* code, size_t* n_words);
-/* `world += Arc<dyn Traced>` (hits.rs:91-95) and native trait objects in general: compiled host code
- * cannot cross to a device.  Always returns OM_ERR_UNSUPPORTED; present so the binding is total.  */
+/* `world += Arc<dyn Traced>` (hits.rs:91-95) for user types described as data (om_dyn_traced): copies n objects.  OM_ERR_INVALID
+ * for a non-finite matrix or coefficient, an all-zero quadric, or clip_lo > clip_hi.                                            */
+OM_API om_status om_scene_add_dyn_traced(om_scene* s, const om_dyn_traced* a, size_t n);
+OM_API om_status om_scene_dyn_traced_count(const om_scene* s, uint64_t* count);
+/* A NATIVE trait object (compiled host code behind `Arc<dyn Traced>` / `Arc<dyn Marched>` that does not describe itself as
+ * om_dyn_traced / om_dyn_marched) cannot cross to a device.  Always returns OM_ERR_UNSUPPORTED; present so the binding is total. */
 OM_API om_status om_scene_add_dyn_object(om_scene* s, const void* trait_object);
 /* counts per list, order: spheres,cubes,triangles,infinite_planes,parallelograms,
  * marched_spheres,marched_boxes,marched_tori */
 OM_API om_status om_scene_counts(const om_scene* s, uint64_t counts[8]);
-/* copy list `which` (0 spheres .. 7 marched_tori, the order of om_scene_counts) back to the caller;
+/* copy list `which` (0 spheres .. 7 marched_tori, the order of om_scene_counts; 8 = the om_dyn_traced objects) back to the caller;
  * nbytes must be count * sizeof(element).  Lets a host hand a generated scene to another consumer. */
 OM_API om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out, size_t nbytes);
 /* HittableList::freeze (hits.rs:87-89).  Builds the BVH that subsumes CameraHash

@@ -41,6 +41,7 @@ def lib():
                     ("marched_tori", A.MarchedTorus)]:
         getattr(L, "omo_scene_add_" + name).argtypes = [vp, P(T), sz]
     L.omo_scene_add_dyn_marched.argtypes = [vp, P(A.DynMarched), P(u32), sz]
+    L.omo_scene_add_dyn_traced.argtypes = [vp, vp, sz]
     L.omo_scene_counts.argtypes = [vp, P(u64)]
     L.omo_scene_random.argtypes = [vp, u64]
     L.omo_scene_basic.argtypes = [vp]
@@ -125,6 +126,12 @@ class OracleScene:
         n = len(arr)
         if n:
             getattr(lib(), "omo_scene_add_" + kind)(self.h, arr, n)
+        return self
+
+    def add_dyn_traced(self, arr):
+        """A ctypes array of om_dyn_traced (Arc<dyn Traced> as data: quadrics)."""
+        if len(arr):
+            lib().omo_scene_add_dyn_traced(self.h, arr, len(arr))
         return self
 
     def add_dyn_marched(self, pod, code):

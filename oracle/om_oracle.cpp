@@ -119,6 +119,17 @@ OMO_API void omo_scene_add_dyn_marched(omo_scene* s, const om_dyn_marched* a, co
     o.world_f = a->world_f; o.code.assign(code, code + n_words); o.material = mat_in(a->material);
     s->w.marched_objects.push_back(o);
 }
+OMO_API void omo_scene_add_dyn_traced(omo_scene* s, const om_dyn_traced* a, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        DynTraced o;
+        o.m_local_to_world = Mat4x4::from_rows16(a[i].m_local_to_world);
+        o.m_word_to_local = Mat4x4::from_rows16(a[i].m_world_to_local);
+        for (int k = 0; k < 10; k++) o.q[k] = a[i].q[k];
+        o.clip_lo = v3(a[i].clip_lo); o.clip_hi = v3(a[i].clip_hi);
+        o.material = mat_in(a[i].material);
+        s->w.traced_objects.push_back(o);
+    }
+}
 OMO_API void omo_scene_counts(const omo_scene* s, uint64_t c[8]) {
     c[0] = s->w.spheres.size(); c[1] = s->w.cubes.size(); c[2] = s->w.triangles.size(); c[3] = s->w.infinite_planes.size();
     c[4] = s->w.parallelograms.size(); c[5] = s->w.marched_spheres.size(); c[6] = s->w.marched_boxes.size(); c[7] = s->w.marched_torus.size();

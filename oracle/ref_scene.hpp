@@ -117,7 +117,7 @@ inline ScatterResult scatter(const Material& m, const Ray& r_in, const HitRecord
 
 // ---- object ids ----------------------------------------------------------------------------
 enum { T_SPHERE = 1, T_CUBE = 2, T_TRIANGLE = 3, T_INFINITE_PLANE = 4, T_PARALLELOGRAM = 5,
-       T_MARCHED_SPHERE = 6, T_MARCHED_BOX = 7, T_MARCHED_TORUS = 8, T_DYN_MARCHED = 9 };
+       T_MARCHED_SPHERE = 6, T_MARCHED_BOX = 7, T_MARCHED_TORUS = 8, T_DYN_MARCHED = 9, T_DYN_TRACED = 10 };
 inline uint64_t make_id(uint32_t type, size_t index) { return ((uint64_t)type << 32) | (uint64_t)(index + 1); }
 
 // ---- traced.rs -----------------------------------------------------------------------------
@@ -386,6 +386,55 @@ struct DynMarched {
 constexpr float HIT_SIZE = 0.001f;  // hits.rs:113
 constexpr int UNSTUCK_MAX_STEPS = 1 << 20;
 
+// Arc<dyn Traced> described as data (include/ottomarcher.h, om_dyn_traced): a quadric q(p) = A x^2 + B y^2 + C z^2 + D xy + E xz + F yz
+// + G x + H y + I z + J in the object's frame, optionally cut by a box of that frame.  The reference has no code for this (the trait is
+// the user's to implement, traced.rs:33-35); the semantics are the header's, stated here a second time in plain C++ in the shape of
+// Sphere::hit (traced.rs:38-63), which it equals bit for bit for the unit sphere.
+struct DynTraced {
+    Mat4x4 m_local_to_world, m_word_to_local;
+    float q[10];
+    Vec3 clip_lo, clip_hi;
+    Material material;
+    bool inside_clip(const Vec3& p) const {
+        return !(p.x() < clip_lo.x() || p.x() > clip_hi.x()) && !(p.y() < clip_lo.y() || p.y() > clip_hi.y()) && !(p.z() < clip_lo.z() || p.z() > clip_hi.z());
+    }
+    bool hit(const Ray& r, float t_min, float t_max, uint64_t id, HitRecord& out) const {
+        const float A = q[0], B = q[1], C = q[2], D = q[3], E = q[4], F = q[5], G = q[6], H = q[7], I = q[8], J = q[9];
+        Ray new_r = r.transform(m_word_to_local);
+        const Vec3 o = new_r.orig, d = new_r.dir;
+        float a = A * d.x() * d.x() + B * d.y() * d.y() + C * d.z() * d.z() + D * d.x() * d.y() + E * d.x() * d.z() + F * d.y() * d.z();
+        float half_b = A * o.x() * d.x() + B * o.y() * d.y() + C * o.z() * d.z()
+                       + 0.5f * (D * (o.x() * d.y() + o.y() * d.x()) + E * (o.x() * d.z() + o.z() * d.x()) + F * (o.y() * d.z() + o.z() * d.y()))
+                       + 0.5f * (G * d.x() + H * d.y() + I * d.z());
+        float c = A * o.x() * o.x() + B * o.y() * o.y() + C * o.z() * o.z() + D * o.x() * o.y() + E * o.x() * o.z() + F * o.y() * o.z() + G * o.x() + H * o.y() + I * o.z() + J;
+        auto ok = [&](float root) { return !(root < t_min || root > t_max) && inside_clip(new_r.at(root)); };
+        float root;
+        if (a == 0.f) {  // the quadric is linear along this ray: one root
+            if (half_b == 0.f) return false;
+            root = -c / (2.f * half_b);
+            if (!ok(root)) return false;
+        } else {
+            float discriminant = half_b * half_b - a * c;
+            if (discriminant < 0.f) return false;
+            float sqrtd = std::sqrt(discriminant);
+            const float s = a < 0.f ? -1.f : 1.f;  // nearer root first, also where the form is negative along the ray
+            root = (-half_b - s * sqrtd) / a;
+            if (!ok(root)) {
+                root = (-half_b + s * sqrtd) / a;
+                if (!ok(root)) return false;
+            }
+        }
+        Vec3 p = new_r.at(root);
+        Vec3 half_grad(A * p.x() + 0.5f * (D * p.y() + E * p.z() + G), B * p.y() + 0.5f * (D * p.x() + F * p.z() + H), C * p.z() + 0.5f * (E * p.x() + F * p.y() + I));
+        out.t = root;
+        out.point = m_local_to_world.dot_p3(p);
+        out.normal = m_local_to_world.dot_v3(half_grad).unit();
+        out.material = material;
+        out.obj_id = id;
+        return true;
+    }
+};
+
 struct World {  // HittableList / FrozenHittableList, hits.rs:37-69 (no dyn lists, no CameraHash)
     std::vector<Sphere> spheres;
     std::vector<Cube> cubes;
@@ -396,6 +445,7 @@ struct World {  // HittableList / FrozenHittableList, hits.rs:37-69 (no dyn list
     std::vector<MarchedBox> marched_boxes;
     std::vector<MarchedTorus> marched_torus;
     std::vector<DynMarched> marched_objects;  // Vec<Arc<dyn Marched>>, scanned after the typed lists (hits.rs:312-320,353-359)
+    std::vector<DynTraced> traced_objects;    // Vec<Arc<dyn Traced>>, scanned after the typed traced lists (hits.rs:280-285)
 
     // counters for the flop accounting of SURVEY.md §8(d); filled when non-null
     struct Counters { uint64_t segments = 0, traced_tests = 0, sdf_evals = 0, normal_evals = 0, march_steps = 0; };
@@ -438,7 +488,8 @@ struct World {  // HittableList / FrozenHittableList, hits.rs:37-69 (no dyn list
         for (size_t i = 0; i < triangles.size(); i++)       if (triangles[i].hit(1, r, t_min, closest_so_far, make_id(T_TRIANGLE, i), hr))             { closest_so_far = hr.t; rec = hr; have = true; }
         for (size_t i = 0; i < infinite_planes.size(); i++) if (plane_hit(infinite_planes[i], r, t_min, closest_so_far, make_id(T_INFINITE_PLANE, i), hr)) { closest_so_far = hr.t; rec = hr; have = true; }
         for (size_t i = 0; i < parallelograms.size(); i++)  if (parallelograms[i].hit(0, r, t_min, closest_so_far, make_id(T_PARALLELOGRAM, i), hr))   { closest_so_far = hr.t; rec = hr; have = true; }
-        if (cn) { cn->segments++; cn->traced_tests += spheres.size() + cubes.size() + triangles.size() + infinite_planes.size() + parallelograms.size(); }
+        for (size_t i = 0; i < traced_objects.size(); i++)  if (traced_objects[i].hit(r, t_min, closest_so_far, make_id(T_DYN_TRACED, i), hr))                { closest_so_far = hr.t; rec = hr; have = true; }
+        if (cn) { cn->segments++; cn->traced_tests += spheres.size() + cubes.size() + triangles.size() + infinite_planes.size() + parallelograms.size() + traced_objects.size(); }
 
         float t = unstuck(t_min, r, cn);
         if (std::isinf(t)) return have;

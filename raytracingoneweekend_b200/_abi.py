@@ -84,11 +84,17 @@ class DynMarched(C.Structure):  # om_dyn_marched: Arc<dyn Marched> as data
                 ("bounds_lo", f32 * 3), ("bounds_hi", f32 * 3), ("material", Material)]
 
 
+class DynTraced(C.Structure):  # om_dyn_traced: Arc<dyn Traced> as data (a quadric in a local frame, optionally clipped)
+    _fields_ = [("m_local_to_world", f32 * 16), ("m_world_to_local", f32 * 16), ("q", f32 * 10), ("clip_lo", f32 * 3), ("clip_hi", f32 * 3),
+                ("bounds_lo", f32 * 3), ("bounds_hi", f32 * 3), ("material", Material)]
+
+
 # local_sdf program opcodes (OM_SDF_*)
 SDF_OPS = {"x": 1, "y": 2, "z": 3, "const": 4, "add": 5, "sub": 6, "mul": 7, "div": 8, "min": 9, "max": 10, "neg": 11, "abs": 12,
            "sqrt": 13, "len2": 14, "len3": 15, "store": 16, "load": 17}
 SDF_STACK, SDF_REGS, SDF_MAX_WORDS = 8, 4, 256
 TYPE_DYN_MARCHED = 9
+TYPE_DYN_TRACED = 10
 
 
 class Camera(C.Structure):
@@ -113,6 +119,7 @@ assert C.sizeof(Sphere) == 152
 assert C.sizeof(Pixel) == 40
 assert C.sizeof(Camera) == 104
 assert C.sizeof(DynMarched) == 180
+assert C.sizeof(DynTraced) == 240
 
 # numpy view of om_pixel (same layout) for vectorised test/bench code
 PIXEL_DTYPE = [("sum", "<f4", (3,)), ("n", "<u4"), ("avg_depth", "<f4"), ("bad_avgs", "<u4"), ("bloom", "<u8"),

@@ -34,6 +34,8 @@ PROTOTYPES = {
     "om_scene_add_marched_tori": ("st", [vp, P(A.MarchedTorus), sz]),
     "om_scene_add_dyn_object": ("st", [vp, vp]),
     "om_scene_add_dyn_marched": ("st", [vp, P(A.DynMarched), P(u32), sz]),
+    "om_scene_add_dyn_traced": ("st", [vp, vp, sz]),
+    "om_scene_dyn_traced_count": ("st", [vp, vp]),
     "om_scene_dyn_marched_count": ("st", [vp, P(u64)]),
     "om_scene_get_dyn_marched": ("st", [vp, u64, P(A.DynMarched), P(u32), P(sz)]),
     "om_scene_counts": ("st", [vp, P(u64)]),

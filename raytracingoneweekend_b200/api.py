@@ -178,6 +178,40 @@ class DynMarched:
         self.code = [int(w) for w in code]
 
 
+class DynTraced:
+    """A user's `impl Traced` (traced.rs:33-35) as data: `world += Arc::new(obj) as Arc<dyn Traced + Send + Sync>` (hits.rs:91-95).
+    The object is a quadric q = (A, B, C, D, E, F, G, H, I, J) in its own frame (see om_dyn_traced in ottomarcher.h), optionally cut
+    by a box of that frame; `bounds` is its world box (None = the trait's "draw always")."""
+
+    def __init__(self, m_local_to_world, q, material, clip=None, bounds=None):
+        inf = float("inf")
+        clo, chi = clip if clip is not None else ((-inf,) * 3, (inf,) * 3)
+        blo, bhi = bounds if bounds is not None else ((-inf,) * 3, (inf,) * 3)
+        self.pod = A.DynTraced(m_local_to_world.e, m_local_to_world.fast_homogenous_inverse().e, (C.c_float * 10)(*[float(x) for x in q]),
+                               _f3(clo), _f3(chi), _f3(blo), _f3(bhi), material)
+
+    @staticmethod
+    def world_box(m_local_to_world, local_lo, local_hi):
+        """BoundingBox3D::new(lo, hi).dot(m) (bounding_box.rs:26-47): the box of the 8 transformed corners."""
+        m = np.array(m_local_to_world.e[:], np.float64).reshape(4, 4)
+        c = np.array([[x, y, z, 1.0] for x in (local_lo[0], local_hi[0]) for y in (local_lo[1], local_hi[1]) for z in (local_lo[2], local_hi[2])])
+        w = (m @ c.T).T[:, :3]
+        return tuple(w.min(axis=0)), tuple(w.max(axis=0))
+
+    @staticmethod
+    def ellipsoid(m_local_to_world, material, bounded=True):
+        """The unit sphere under an affine map: the same surface, and the same bits, as Sphere::new(m, material)."""
+        b = DynTraced.world_box(m_local_to_world, (-1, -1, -1), (1, 1, 1)) if bounded else None
+        return DynTraced(m_local_to_world, (1, 1, 1, 0, 0, 0, 0, 0, 0, -1), material, bounds=b)
+
+    @staticmethod
+    def cylinder(m_local_to_world, material, half_height=1.0):
+        """x^2 + z^2 = 1 for |y| <= half_height (an open tube)."""
+        h = float(half_height)
+        return DynTraced(m_local_to_world, (1, 0, 1, 0, 0, 0, 0, 0, 0, -1), material, clip=((-2, -h, -2), (2, h, 2)),
+                         bounds=DynTraced.world_box(m_local_to_world, (-1, -h, -1), (1, h, 1)))
+
+
 class Camera:
     @staticmethod
     def new(lookfrom, lookat, vup, vfov_in_degrees, aspect_ratio, aperture, focus_dist):
@@ -204,6 +238,7 @@ class HittableList:
     def __init__(self):
         self.lists = {k: [] for k in _LISTS}
         self.dyn_marched = []  # marched_objects: Vec<Arc<dyn Marched>> (DynMarched)
+        self.dyn_traced = []   # traced_objects: Vec<Arc<dyn Traced>> (DynTraced)
         self._generated = []  # (kind, seed, n) requests replayed into the C scene
 
     def clear(self):
@@ -216,8 +251,10 @@ class HittableList:
             self.lists[_KIND_OF[type(obj)]].append(obj)
         elif isinstance(obj, DynMarched):
             self.dyn_marched.append(obj)
+        elif isinstance(obj, DynTraced):
+            self.dyn_traced.append(obj)
         else:
-            # native trait objects (Arc<dyn Traced>, compiled Marched impls): the ABI reports OM_ERR_UNSUPPORTED
+            # native trait objects (compiled Traced / Marched impls that do not describe themselves as data): the ABI reports OM_ERR_UNSUPPORTED
             h = C.c_void_p()
             _lib.call("om_scene_create", C.byref(h))
             try:
@@ -242,6 +279,9 @@ class HittableList:
         for d in self.dyn_marched:
             code = (C.c_uint32 * max(1, len(d.code)))(*d.code)
             _lib.call("om_scene_add_dyn_marched", s.h, C.byref(d.pod), code, len(d.code))
+        if self.dyn_traced:
+            arr = (A.DynTraced * len(self.dyn_traced))(*[d.pod for d in self.dyn_traced])
+            _lib.call("om_scene_add_dyn_traced", s.h, arr, len(arr))
         _lib.call("om_scene_freeze", s.h, C.byref(cam) if cam is not None else None, flags)
         return s
 
@@ -280,6 +320,14 @@ class FrozenHittableList:
             _lib.call("om_scene_get_list", self.h, i, arr, C.sizeof(arr))
             out[name] = arr
         return out
+
+    def dyn_traced(self):
+        """ctypes array of the om_dyn_traced objects in list order."""
+        n = C.c_uint64()
+        _lib.call("om_scene_dyn_traced_count", self.h, C.byref(n))
+        arr = (A.DynTraced * n.value)()
+        _lib.call("om_scene_get_list", self.h, 8, arr, C.sizeof(arr))
+        return arr
 
     def dyn_marched(self):
         """[(om_dyn_marched, program words)] in list order."""

@@ -229,7 +229,7 @@ om_status om_scene_clear(om_scene* s) {
     om_status NAME(om_scene* s, const TYPE* a, size_t n) {                                          \
         if (!s || (!a && n)) return fail(OM_ERR_INVALID, #NAME ": NULL argument");                  \
         if (s->frozen) return fail(OM_ERR_INVALID, #NAME ": scene is frozen (om_scene_clear first)"); \
-        if (s->lists.FIELD.size() + n > 0x0FFFFFFFull) return fail(OM_ERR_INVALID, #NAME ": too many objects"); \
+        if (s->lists.FIELD.size() + n > uint64_t(omd::REF_MAX_OBJECTS)) return fail(OM_ERR_INVALID, #NAME ": too many objects"); \
         s->lists.FIELD.insert(s->lists.FIELD.end(), a, a + n);                                      \
         return OM_OK;                                                                               \
     }
@@ -247,11 +247,27 @@ om_status om_scene_add_dyn_marched(om_scene* s, const om_dyn_marched* obj, const
     const char* why = omh::check_sdf_program(code, n_words);
     if (why[0]) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: %s", why);
     omh::SceneLists& L = s->lists;
-    if (L.dyn_marched.size() + 1 > 0x0FFFFFFFull || L.dyn_code.size() + n_words > 0x3FFFFFFFull) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: too many objects");
+    if (L.dyn_marched.size() + 1 > uint64_t(omd::REF_MAX_OBJECTS) || L.dyn_code.size() + n_words > 0x3FFFFFFFull) return fail(OM_ERR_INVALID, "om_scene_add_dyn_marched: too many objects");
     if (L.dyn_code_first.empty()) L.dyn_code_first.push_back(0u);
     L.dyn_marched.push_back(*obj);
     L.dyn_code.insert(L.dyn_code.end(), code, code + n_words);
     L.dyn_code_first.push_back(uint32_t(L.dyn_code.size()));
+    return OM_OK;
+}
+om_status om_scene_add_dyn_traced(om_scene* s, const om_dyn_traced* a, size_t n) {
+    if (!s || (!a && n)) return fail(OM_ERR_INVALID, "om_scene_add_dyn_traced: NULL argument");
+    if (s->frozen) return fail(OM_ERR_INVALID, "om_scene_add_dyn_traced: scene is frozen (om_scene_clear first)");
+    if (s->lists.dyn_traced.size() + n > uint64_t(omd::REF_MAX_OBJECTS)) return fail(OM_ERR_INVALID, "om_scene_add_dyn_traced: too many objects");
+    for (size_t i = 0; i < n; i++) {
+        const char* why = omh::check_dyn_traced(a[i]);
+        if (why[0]) return fail(OM_ERR_INVALID, "om_scene_add_dyn_traced: object %zu: %s", i, why);
+    }
+    s->lists.dyn_traced.insert(s->lists.dyn_traced.end(), a, a + n);
+    return OM_OK;
+}
+om_status om_scene_dyn_traced_count(const om_scene* s, uint64_t* count) {
+    if (!s || !count) return fail(OM_ERR_INVALID, "om_scene_dyn_traced_count: NULL argument");
+    *count = s->lists.dyn_traced.size();
     return OM_OK;
 }
 om_status om_scene_dyn_marched_count(const om_scene* s, uint64_t* count) {
@@ -295,6 +311,7 @@ om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out, size_t
         case 5: src = L.marched_spheres.data(); have = L.marched_spheres.size() * sizeof(om_marched_sphere); break;
         case 6: src = L.marched_boxes.data(); have = L.marched_boxes.size() * sizeof(om_marched_box); break;
         case 7: src = L.marched_tori.data(); have = L.marched_tori.size() * sizeof(om_marched_torus); break;
+        case 8: src = L.dyn_traced.data(); have = L.dyn_traced.size() * sizeof(om_dyn_traced); break;
         default: return fail(OM_ERR_INVALID, "om_scene_get_list: list %u does not exist", which);
     }
     if (nbytes != have) return fail(OM_ERR_INVALID, "om_scene_get_list: nbytes %zu != %zu", nbytes, have);
@@ -304,7 +321,7 @@ om_status om_scene_get_list(const om_scene* s, uint32_t which, void* out, size_t
 om_status om_scene_generate(om_scene* s, uint32_t kind, uint64_t seed, uint64_t n_param) {
     if (!s) return fail(OM_ERR_INVALID, "om_scene_generate: NULL scene");
     if (s->frozen) return fail(OM_ERR_INVALID, "om_scene_generate: scene is frozen");
-    if (kind == 5 && n_param > 0x0FFFFFF0ull) return fail(OM_ERR_INVALID, "om_scene_generate: too many spheres");
+    if (kind == 5 && n_param > uint64_t(omd::REF_MAX_OBJECTS) - 16u) return fail(OM_ERR_INVALID, "om_scene_generate: too many spheres");
     if (!omh::generate(s->lists, kind, seed, n_param)) return fail(OM_ERR_INVALID, "om_scene_generate: unknown kind %u", kind);
     return OM_OK;
 }

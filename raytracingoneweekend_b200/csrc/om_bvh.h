@@ -17,7 +17,7 @@ struct Aabb {
 
 // 64-byte node: both children's boxes + child references (one shared-memory fetch per visit).
 // child >= 0: index of an inner node; child < 0: leaf, ~child is the primitive reference
-// (prim type code << 28 | index).  An empty child has an inverted box and is never entered.
+// (omd::make_ref: type code << 27 | index, always below 2^31 so that ~ref is negative).  An empty child has an inverted box and is never entered.
 struct alignas(16) Node {
     float lmin[3], lmax[3], rmin[3], rmax[3];
     int32_t left, right;

@@ -239,6 +239,42 @@ __device__ __forceinline__ bool cube_t(float4 r0, float4 r1, float4 r2, const Ra
     return true;
 }
 
+// om_dyn_traced (include/ottomarcher.h): a user's `impl Traced` described as a quadric in its own frame, optionally cut by a box of
+// that frame.  Sphere::hit's arithmetic (traced.rs:38-56) generalised term by term, so that the unit sphere gives Sphere::hit's bits.
+// qa = {A,B,C,D} qb = {E,F,G,H} qc = {I,J,clip_lo.x,clip_lo.y} qd = {clip_lo.z,clip_hi.xyz}
+__device__ __forceinline__ bool quadric_t(float4 r0, float4 r1, float4 r2, float4 qa, float4 qb, float4 qc, float4 qd, const Ray& r, float t_min, float t_max, float& t_out) {
+    const V3 o = xf_point(r0, r1, r2, r.o), d = xf_vec(r0, r1, r2, r.d);
+    const float A = qa.x, B = qa.y, C = qa.z, D = qa.w, E = qb.x, F = qb.y, G = qb.z, H = qb.w, I = qc.x, J = qc.y;
+    const float a = A * d.x * d.x + B * d.y * d.y + C * d.z * d.z + D * d.x * d.y + E * d.x * d.z + F * d.y * d.z;
+    const float half_b = A * o.x * d.x + B * o.y * d.y + C * o.z * d.z + 0.5f * (D * (o.x * d.y + o.y * d.x) + E * (o.x * d.z + o.z * d.x) + F * (o.y * d.z + o.z * d.y)) +
+                         0.5f * (G * d.x + H * d.y + I * d.z);
+    const float c = A * o.x * o.x + B * o.y * o.y + C * o.z * o.z + D * o.x * o.y + E * o.x * o.z + F * o.y * o.z + G * o.x + H * o.y + I * o.z + J;
+    Ray lr;
+    lr.o = o; lr.d = d;
+    auto ok = [&](float root) {
+        const V3 p = ray_at(lr, root);
+        return !(root < t_min || root > t_max) && !(p.x < qc.z || p.x > qd.y) && !(p.y < qc.w || p.y > qd.z) && !(p.z < qd.x || p.z > qd.w);
+    };
+    float root;
+    if (a == 0.f) {  // the quadric is linear along this ray: one root
+        if (half_b == 0.f) return false;
+        root = -c / (2.f * half_b);
+        if (!ok(root)) return false;
+    } else {
+        const float discriminant = half_b * half_b - a * c;
+        if (discriminant < 0.f) return false;
+        const float sqrtd = sqrtf(discriminant);
+        const float s = a < 0.f ? -1.f : 1.f;  // nearer root first, also where the form is negative along the ray
+        root = (-half_b - s * sqrtd) / a;
+        if (!ok(root)) {
+            root = (-half_b + s * sqrtd) / a;
+            if (!ok(root)) return false;
+        }
+    }
+    t_out = root;
+    return true;
+}
+
 // ---- closest hit over the traced primitives ------------------------------------------------
 struct Best {
     float t;
@@ -263,6 +299,9 @@ __device__ __forceinline__ void test_prim(const SceneView<SMEM>& sv, const Scene
     } else if (type == omd::PT_PLANE) {
         const uint32_t u = S.off_hot[omd::PT_PLANE] + omd::U_PLANE * i;
         if (plane_t(sv.hot(u), sv.hot(u + 1), r, t_min, best.t, t)) accept(best, t, ref);
+    } else if (type == omd::PT_TDYN) {
+        const uint32_t u = S.off_hot[omd::PT_TDYN] + omd::U_TDYN * i;
+        if (quadric_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), sv.hot(u + 3), sv.hot(u + 4), sv.hot(u + 5), sv.hot(u + 6), r, t_min, best.t, t)) accept(best, t, ref);
     } else {
         const uint32_t u = S.off_hot[type] + omd::U_BARY * i;
         if (bary_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), sv.hot(u + 3), type == omd::PT_TRI, r, t_min, best.t, t)) accept(best, t, ref);
@@ -368,6 +407,7 @@ __device__ __forceinline__ uint32_t linear_ref(const SceneView<SMEM>& sv, const 
     if (brute) {
         uint32_t type = 0;
         while (type < 4u && k >= S.n[type]) { k -= S.n[type]; type++; }
+        if (type == 4u && k >= S.n[4]) { k -= S.n[4]; type = omd::PT_TDYN; }  // traced_objects come after the typed lists (hits.rs:280-285)
         return omd::make_ref(type, k);
     }
     const float4 q = sv.hot(S.off_large + (k >> 2));
@@ -433,7 +473,7 @@ __device__ __forceinline__ Best closest_traced_warp(const SceneView<SMEM>& sv, c
     Best best;
     best.t = t_max;
     best.ref = omd::REF_NONE;
-    const uint32_t n_lin = brute ? (S.n[0] + S.n[1] + S.n[2] + S.n[3] + S.n[4]) : S.n_large;
+    const uint32_t n_lin = brute ? (S.n[0] + S.n[1] + S.n[2] + S.n[3] + S.n[4] + S.n[omd::PT_TDYN]) : S.n_large;
     const bool have_bvh = !brute && S.n_nodes > 0u;
     const RayInv q = ray_inv(r);
     const float pad = S.dyn_pad;
@@ -892,6 +932,16 @@ __device__ __forceinline__ void finish_hit(const SceneView<SMEM>& sv, const Scen
         const float div = om::dot(n, r.d);
         h.point = ray_at(r, h.t);
         h.normal = n * copysignf(1.f, -div);
+    } else if (type == omd::PT_TDYN) {  // om_dyn_traced: point = M . p_local, normal = unit(M . grad q / 2), as Sphere and Cube carry theirs (traced.rs:57-61,290-297)
+        const uint32_t u = S.off_hot[omd::PT_TDYN] + omd::U_TDYN * i;
+        const float4 r0 = sv.hot(u), r1 = sv.hot(u + 1), r2 = sv.hot(u + 2), qa = sv.hot(u + 3), qb = sv.hot(u + 4), qc = sv.hot(u + 5);
+        Ray lr; lr.o = xf_point(r0, r1, r2, r.o); lr.d = xf_vec(r0, r1, r2, r.d);
+        const V3 p = ray_at(lr, h.t);
+        const V3 half_grad = v3(qa.x * p.x + 0.5f * (qa.w * p.y + qb.x * p.z + qb.z), qa.y * p.y + 0.5f * (qa.w * p.x + qb.y * p.z + qb.w), qa.z * p.z + 0.5f * (qb.x * p.x + qb.y * p.y + qc.x));
+        const uint32_t c = S.off_tdyn_l2w + omd::U_XF * i;
+        const float4 m0 = sv.cold(c), m1 = sv.cold(c + 1), m2 = sv.cold(c + 2);
+        h.point = xf_point(m0, m1, m2, p);
+        h.normal = om::unit(xf_vec(m0, m1, m2, half_grad));
     } else if (type == omd::PT_TRI || type == omd::PT_PARA) {  // traced.rs:198-199
         const uint32_t u = S.off_hot[type] + omd::U_BARY * i;
         const float4 b = sv.hot(u + 1);

@@ -3,6 +3,7 @@
 // them (the Rust host, this mirror, or the test oracle).
 #include "om_host.h"
 
+#include <cmath>
 #include <math.h>
 #include <string.h>
 
@@ -372,6 +373,17 @@ bool generate(SceneLists& s, uint32_t kind, uint64_t seed, uint64_t n_param) {
 // om_scene_add_dyn_marched: the program must keep the operand stack within [0, OM_SDF_STACK], end with one value,
 // name existing registers and read them only after a write.  The device interpreter (om_device.cuh, sdf_program) and
 // the oracle's rely on this check instead of guarding every step.
+const char* check_dyn_traced(const om_dyn_traced& o) {
+    for (int i = 0; i < 16; i++) if (!std::isfinite(o.m_local_to_world[i]) || !std::isfinite(o.m_world_to_local[i])) return "non-finite matrix entry";
+    bool any = false;
+    for (int i = 0; i < 10; i++) { if (!std::isfinite(o.q[i])) return "non-finite quadric coefficient"; if (i < 9 && o.q[i] != 0.f) any = true; }
+    if (!any) return "the quadric has no term in x, y, z";
+    for (int a = 0; a < 3; a++) {
+        if (std::isnan(o.clip_lo[a]) || std::isnan(o.clip_hi[a]) || o.clip_lo[a] > o.clip_hi[a]) return "clip_lo > clip_hi (or NaN)";
+        if (std::isnan(o.bounds_lo[a]) || std::isnan(o.bounds_hi[a]) || o.bounds_lo[a] > o.bounds_hi[a]) return "bounds_lo > bounds_hi (or NaN)";
+    }
+    return "";
+}
 const char* check_sdf_program(const uint32_t* code, size_t n_words) {
     if (n_words == 0 || n_words > OM_SDF_MAX_WORDS) return "program must have 1..OM_SDF_MAX_WORDS words";
     int depth = 0;

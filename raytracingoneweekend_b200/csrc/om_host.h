@@ -65,7 +65,11 @@ struct SceneLists {  // HittableList, hits.rs:37-43
     // marched_objects: Vec<Arc<dyn Marched>> as data (om_dyn_marched); object i's program = dyn_code[dyn_code_first[i] .. dyn_code_first[i + 1])
     std::vector<om_dyn_marched> dyn_marched;
     std::vector<uint32_t> dyn_code, dyn_code_first;
+    // traced_objects: Vec<Arc<dyn Traced>> as data (om_dyn_traced: quadrics in a local frame), scanned after the parallelograms
+    std::vector<om_dyn_traced> dyn_traced;
 };
+// "" when the description is usable (see om_scene_add_dyn_traced), else what is wrong with it
+const char* check_dyn_traced(const om_dyn_traced& o);
 // "" when the program is well-formed (see om_scene_add_dyn_marched), else what is wrong with it
 const char* check_sdf_program(const uint32_t* code, size_t n_words);
 bool generate(SceneLists& s, uint32_t kind, uint64_t seed, uint64_t n_param);

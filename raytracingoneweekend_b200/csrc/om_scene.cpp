@@ -90,6 +90,23 @@ Aabb bary_box(const om_barycentric& b, bool parallelogram, double reach) {
     }
     return padded(lo, hi, extra);
 }
+// om_dyn_traced: the user's world box (Bounded::build_world_bounding_box), widened because the f32 quadric test - like Sphere::hit,
+// whose arithmetic it shares - reports hits for rays that pass slightly outside the exact surface; the same fattening as a sphere
+// of the object's smallest scale, applied to the box's half extents.  A box that is not finite sends the object to the always-test list.
+bool dyn_traced_bounded(const om_dyn_traced& o) {
+    for (int a = 0; a < 3; a++) if (!std::isfinite(o.bounds_lo[a]) || !std::isfinite(o.bounds_hi[a])) return false;
+    return true;
+}
+Aabb dyn_traced_box(const om_dyn_traced& o, double reach) {
+    const double rho = reach / col_norm_min(o.m_local_to_world);
+    const double fat = std::sqrt(1.0 + kSphereK * rho * rho) - 1.0;
+    double lo[3], hi[3], extra[3];
+    for (int a = 0; a < 3; a++) {
+        lo[a] = o.bounds_lo[a]; hi[a] = o.bounds_hi[a];
+        extra[a] = (0.5 * (hi[a] - lo[a]) + 1e-3) * (fat + 0.01);
+    }
+    return padded(lo, hi, extra);
+}
 // Distance-proportional padding.  Each margin above that depends on `reach` is at most slope * D, D = distance from
 // the ray origin to the object's centre (sphere: r*(sqrt(1+K*(D/r)^2)-1) <= sqrt(K)*D; cube and triangle: linear in D
 // by construction), times the object's anisotropy (largest world half extent / smallest scale).  A traversal that
@@ -358,6 +375,7 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     h.n[PT_MSPHERE] = uint32_t(L.marched_spheres.size()); h.n[PT_MBOX] = uint32_t(L.marched_boxes.size());
     h.n[PT_MTORUS] = uint32_t(L.marched_tori.size());
     h.n[PT_MDYN] = uint32_t(L.dyn_marched.size());
+    h.n[PT_TDYN] = uint32_t(L.dyn_traced.size());
     out.n_total = 0;
     for (uint32_t i = 0; i < PT_COUNT; i++) out.n_total += h.n[i];
 
@@ -403,20 +421,24 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
         for (const om_sphere& o : L.spheres) slope = std::max(slope, std::sqrt(kSphereK) * aniso(o.m_local_to_world));
         for (const om_cube& o : L.cubes) slope = std::max(slope, 2.0 * kCubeSlope * aniso(o.m_local_to_world));
         if (!L.triangles.empty() || !L.parallelograms.empty()) slope = std::max(slope, kBarySlope);
+        for (const om_dyn_traced& o : L.dyn_traced) slope = std::max(slope, std::sqrt(kSphereK) * aniso(o.m_local_to_world));
         h.dyn_pad = float(slope * 1.01);
         if (!(h.dyn_pad > 0.f) || !std::isfinite(h.dyn_pad)) { dyn = false; h.dyn_pad = 0.f; }
     }
     if (dyn) reach = 0.0;
     std::vector<uint32_t> refs;
     std::vector<Aabb> boxes;
-    refs.reserve(L.spheres.size() + L.cubes.size() + L.triangles.size() + L.parallelograms.size());
+    refs.reserve(L.spheres.size() + L.cubes.size() + L.triangles.size() + L.parallelograms.size() + L.dyn_traced.size());
     boxes.reserve(refs.capacity());
     for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i], reach)); }
     for (size_t i = 0; i < L.cubes.size(); i++) { refs.push_back(make_ref(PT_CUBE, uint32_t(i))); boxes.push_back(cube_box(L.cubes[i], reach)); }
     for (size_t i = 0; i < L.triangles.size(); i++) { refs.push_back(make_ref(PT_TRI, uint32_t(i))); boxes.push_back(bary_box(L.triangles[i], false, reach)); }
     for (size_t i = 0; i < L.parallelograms.size(); i++) { refs.push_back(make_ref(PT_PARA, uint32_t(i))); boxes.push_back(bary_box(L.parallelograms[i], true, reach)); }
+    for (size_t i = 0; i < L.dyn_traced.size(); i++)
+        if (dyn_traced_bounded(L.dyn_traced[i])) { refs.push_back(make_ref(PT_TDYN, uint32_t(i))); boxes.push_back(dyn_traced_box(L.dyn_traced[i], reach)); }
     std::vector<uint32_t> large;
     for (size_t i = 0; i < L.infinite_planes.size(); i++) large.push_back(make_ref(PT_PLANE, uint32_t(i)));  // Bounded default: +-INF (bounding_box.rs:69-73)
+    for (size_t i = 0; i < L.dyn_traced.size(); i++) if (!dyn_traced_bounded(L.dyn_traced[i])) large.push_back(make_ref(PT_TDYN, uint32_t(i)));
     if (!(flags & 1u) && refs.size() > 4) {
         // An object whose box is a large share of the whole scene (the r=1000 ground sphere,
         // main.rs:41) overlaps every subtree: test it once per ray instead.
@@ -482,6 +504,14 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     for (const om_infinite_plane& p : L.infinite_planes) { hot.f4(p.normal[0], p.normal[1], p.normal[2], 0.f); hot.f4(p.center[0], p.center[1], p.center[2], 0.f); }
     h.off_hot[PT_PARA] = hot.units();
     for (const om_barycentric& b : L.parallelograms) pack_bary(b);
+    h.off_hot[PT_TDYN] = hot.units();
+    for (const om_dyn_traced& o : L.dyn_traced) {
+        hot.rows3(o.m_world_to_local);
+        hot.f4(o.q[0], o.q[1], o.q[2], o.q[3]);
+        hot.f4(o.q[4], o.q[5], o.q[6], o.q[7]);
+        hot.f4(o.q[8], o.q[9], o.clip_lo[0], o.clip_lo[1]);
+        hot.f4(o.clip_lo[2], o.clip_hi[0], o.clip_hi[1], o.clip_hi[2]);
+    }
     h.off_large = hot.units();
     for (size_t i = 0; i < large.size(); i += 4) {
         uint32_t q[4] = {REF_NONE, REF_NONE, REF_NONE, REF_NONE};
@@ -572,6 +602,8 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     for (const om_sphere& s : L.spheres) cold.rows3(s.m_local_to_world);
     h.off_cube_l2w = cold.units();
     for (const om_cube& s : L.cubes) cold.rows3(s.m_local_to_world);
+    h.off_tdyn_l2w = cold.units();
+    for (const om_dyn_traced& o : L.dyn_traced) cold.rows3(o.m_local_to_world);
     h.off_mat = cold.units();
     uint32_t base = 0;
     auto mats = [&](uint32_t pt, auto const& list) {
@@ -582,6 +614,7 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
     mats(PT_PARA, L.parallelograms); mats(PT_MSPHERE, L.marched_spheres); mats(PT_MBOX, L.marched_boxes); mats(PT_MTORUS, L.marched_tori);
     mats(PT_MDYN, L.dyn_marched);
+    mats(PT_TDYN, L.dyn_traced);
     lap("pack hot + cold images");
     // The candidate grid and the distance BVH need analytic bounds of every |sdf|; a user program has none, so a scene
     // with dyn marched objects is marched by the plain scan (hits.rs:301-320).

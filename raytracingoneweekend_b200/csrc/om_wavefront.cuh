@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 2) k_wf_extend(const __grid_co
     const uint32_t* __restrict__ q_in = W.q_ray[W.it & 1u];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t n_lin = brute ? (S.n[0] + S.n[1] + S.n[2] + S.n[3] + S.n[4]) : S.n_large;
+    const uint32_t n_lin = brute ? (S.n[0] + S.n[1] + S.n[2] + S.n[3] + S.n[4] + S.n[omd::PT_TDYN]) : S.n_large;
     const bool have_bvh = !brute && S.n_nodes > 0u;
     const bool have_marched = S.n_marched != 0u;
     Counters cn = {0, 0, 0, 0, 0, 0, 0};

@@ -79,7 +79,7 @@ def test_extern_block_matches_header_and_library(api):
 def test_struct_sizes_and_offsets_equal_the_ctypes_mirrors(A):
     structs = rust_structs(open(os.path.join(RUST, "src", "ffi.rs")).read())
     mirrors = {"om_material": A.Material, "om_sphere": A.Sphere, "om_cube": A.Cube, "om_infinite_plane": A.InfinitePlane, "om_barycentric": A.Barycentric,
-               "om_marched_sphere": A.MarchedSphere, "om_marched_box": A.MarchedBox, "om_marched_torus": A.MarchedTorus, "om_dyn_marched": A.DynMarched,
+               "om_marched_sphere": A.MarchedSphere, "om_marched_box": A.MarchedBox, "om_marched_torus": A.MarchedTorus, "om_dyn_marched": A.DynMarched, "om_dyn_traced": A.DynTraced,
                "om_camera": A.Camera, "om_pixel": A.Pixel, "om_render_params": A.RenderParams}
     assert set(mirrors) == set(structs), set(mirrors) ^ set(structs)
     cache = {}
