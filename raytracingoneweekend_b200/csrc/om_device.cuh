@@ -767,6 +767,12 @@ __device__ __noinline__ float abs_sdf_of(SceneView<SMEM> sv, const SceneHeader& 
 // cache) meet at a named barrier at the top of the path loop and again between the closest-hit query and shading, so that
 // they stream the same part of this 70 KB kernel at the same time.  The count variant also tells the warps that ran out of
 // tickets when the last warp of their group has left the loop.
+#ifndef OM_MARCH_STEPS
+#define OM_MARCH_STEPS 16  // bounded marching: sphere-tracing steps per path-loop iteration
+#endif
+#ifndef OM_BOUNDED_MARCH_ALL
+#define OM_BOUNDED_MARCH_ALL 0  // 1: also in the kernel of scenes without marched structures (experiment)
+#endif
 #ifndef OM_GROUP_TICKETS
 #define OM_GROUP_TICKETS 8
 #endif
@@ -847,6 +853,50 @@ __device__ __noinline__ Hit march(SceneView<SMEM> sv, const SceneHeader& S, Ray 
     }
     return out;
 }
+
+// hits.rs:288-365 in instalments: the same steps in the same order as march() above, at most `steps` sphere-tracing
+// iterations per call.  Returns true when the march is over: out.ref is the marched hit, or REF_NONE = the traced record stands.
+template <bool SMEM, bool COUNT, bool ACCEL, bool DYN>
+__device__ __noinline__ bool march_some(SceneView<SMEM> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, float& t, uint32_t& left, int steps,
+                                        Hit& out, Counters* cn) {
+    int2 stk[ACCEL ? MSTACK : 1];
+    out.t = closest; out.ref = omd::REF_NONE; out.point = v3(0.f, 0.f, 0.f); out.normal = v3(0.f, 0.f, 0.f);
+    if (left == 0xFFFFFFFFu) {  // unstuck
+        if (COUNT) cn->march_entered++;
+        const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
+        float new_t = t_min;
+        const Near n0 = ACCEL ? nearest_marched_accel(sv, S, ray_at(r, t_min), stk) : nearest_marched<SMEM, DYN>(sv, S, ray_at(r, t_min));
+        if (COUNT) cn->sdf_evals += n0.evals;
+        if (n0.ref == omd::REF_NONE) return true;
+        float aux = n0.d;
+        int k = 0;
+        while (aux < HIT_SIZE && k < UNSTUCK_MAX_STEPS) {
+            new_t += MIN_STEP_SIZE;
+            aux = abs_sdf_of<SMEM, DYN>(sv, S, n0.ref, ray_at(r, new_t));
+            k++;
+            if (COUNT) cn->sdf_evals++;
+        }
+        t = new_t;
+        left = 1024u;
+    }
+    while (t < t_max && t < closest && left > 0u) {
+        if (steps-- <= 0) return false;
+        left--;
+        const V3 point = ray_at(r, t);
+        const Near n = ACCEL ? nearest_marched_accel(sv, S, point, stk) : nearest_marched<SMEM, DYN>(sv, S, point);
+        if (COUNT) { cn->march_steps++; cn->sdf_evals += n.evals; }
+        if (n.ref == omd::REF_NONE) return true;
+        if (n.d < HIT_SIZE) {
+            out.t = t; out.ref = n.ref; out.point = point;
+            out.normal = marched_normal<SMEM, DYN>(sv, S, n.ref, point);
+            if (COUNT) cn->normal_evals++;
+            return true;
+        }
+        t += n.d;
+    }
+    return true;
+}
+
 
 // FrozenHittableList::hit (hits.rs:270-334); also first_hit (the BVH subsumes CameraHash).
 // Warp-collective: all 32 lanes call it, `alive` marks the lanes that carry a ray.
@@ -1144,6 +1194,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
     const bool brute = (A.flags & OM_RENDER_BRUTE_FORCE) != 0;
     const bool adaptive = (A.flags & OM_RENDER_ADAPTIVE) != 0;
     const bool align = (A.flags & OM_RENDER_PHASE_ALIGN) != 0;
+    constexpr bool BOUNDED = OM_BOUNDED_MARCH_ALL || MA == 1 || MA == 3;  // scenes built around marched objects (C3); C2's kernel keeps march()
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
     unsigned long long credited = 0, traced = 0;
     uint32_t warp_iters = 0, lane_iters = 0;  // COUNT: lane occupancy of the path loop
@@ -1219,6 +1270,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         float first_t = kInf;
         uint32_t first_lo = 0, first_hi = 0;
         bool fresh = true;
+        bool marching = false;          // BOUNDED: the lane's ray is part-way through its march
+        float m_t = 0.f, pend_t = 0.f;  // ... how far, and the traced hit that stands if the march finds nothing
+        uint32_t m_left = 0xFFFFFFFFu, pend_ref = omd::REF_NONE;
         while (__any_sync(FULL, todo > 0u)) {
             const bool alive = todo > 0u;
             if (COUNT) { warp_iters++; lane_iters += alive ? 1u : 0u; }
@@ -1231,9 +1285,36 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
                 seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
                 fresh = false;
             }
-            Hit h = closest_hit_warp<SMEM, COUNT, MA>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
+            Hit h;
+            bool resolved = alive;  // this lane's segment is resolved in this iteration (shade it)
+            if constexpr (BOUNDED) {
+                // Bounded marching: a lane whose ray enters the marched objects' bounds sphere-traces at most OM_MARCH_STEPS steps per
+                // iteration and carries on in the next one, while the other lanes of the warp shade, start samples and traverse.
+                // (One call of march() ran as long as the warp's longest march: 5.6 of 32 lanes per instruction on C3.)
+                const bool trav = alive && !marching;
+                if (COUNT && trav) cn.segments++;
+                const Best b = closest_traced_warp<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, trav, cn, stack);
+                h.t = pend_t; h.ref = pend_ref; h.point = v3(0.f, 0.f, 0.f); h.normal = v3(0.f, 0.f, 0.f);
+                if (trav) {
+                    h.t = b.t; h.ref = b.ref;
+                    if (S.n_marched != 0u) {  // (see closest_hit_warp)
+                        const RayInv q = ray_inv(ray);
+                        if (slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, A.tmin, fminf(A.tmax, b.t)) < kInf) {
+                            marching = true; m_left = 0xFFFFFFFFu; m_t = 0.f; pend_t = b.t; pend_ref = b.ref;
+                        }
+                    }
+                }
+                if (alive && marching) {
+                    Hit m;
+                    const bool over = march_some<SMEM, COUNT, MA == 1, MA == 3>(sv, S, ray, A.tmin, A.tmax, pend_t, m_t, m_left, OM_MARCH_STEPS, m, &cn);
+                    resolved = over;
+                    if (over) { marching = false; if (m.ref != omd::REF_NONE) h = m; else { h.t = pend_t; h.ref = pend_ref; } }
+                }
+            } else {
+                h = closest_hit_warp<SMEM, COUNT, MA>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
+            }
             if (align) phase_bar();
-            if (alive) {
+            if (resolved) {
                 bool finished;
                 V3 result = color;
                 if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116

@@ -83,49 +83,6 @@ __device__ __forceinline__ void pool_push(uint16_t* q, uint32_t* n, bool pred, u
     if (pred) q[base + (uint32_t)__popc(m & ((1u << lane) - 1u))] = (uint16_t)s;
 }
 
-// hits.rs:288-365 in instalments: the same steps in the same order as march() (om_device.cuh), at most `steps` sphere-tracing
-// iterations per call.  Returns true when the march is over: out.ref is the marched hit, or REF_NONE = the traced record stands.
-template <bool COUNT, bool ACCEL, bool DYN>
-__device__ __noinline__ bool pool_march(SceneView<true> sv, const SceneHeader& S, Ray r, float t_min, float t_max, float closest, float& t, uint32_t& left, int steps,
-                                        Hit& out, Counters* cn) {
-    int2 stk[ACCEL ? MSTACK : 1];
-    out.t = closest; out.ref = omd::REF_NONE; out.point = v3(0.f, 0.f, 0.f); out.normal = v3(0.f, 0.f, 0.f);
-    if (left == 0xFFFFFFFFu) {  // unstuck
-        if (COUNT) cn->march_entered++;
-        const float MIN_STEP_SIZE = HIT_SIZE / 2.f;
-        float new_t = t_min;
-        const Near n0 = ACCEL ? nearest_marched_accel(sv, S, ray_at(r, t_min), stk) : nearest_marched<true, DYN>(sv, S, ray_at(r, t_min));
-        if (COUNT) cn->sdf_evals += n0.evals;
-        if (n0.ref == omd::REF_NONE) return true;
-        float aux = n0.d;
-        int k = 0;
-        while (aux < HIT_SIZE && k < UNSTUCK_MAX_STEPS) {
-            new_t += MIN_STEP_SIZE;
-            aux = abs_sdf_of<true, DYN>(sv, S, n0.ref, ray_at(r, new_t));
-            k++;
-            if (COUNT) cn->sdf_evals++;
-        }
-        t = new_t;
-        left = 1024u;
-    }
-    while (t < t_max && t < closest && left > 0u) {
-        if (steps-- <= 0) return false;
-        left--;
-        const V3 point = ray_at(r, t);
-        const Near n = ACCEL ? nearest_marched_accel(sv, S, point, stk) : nearest_marched<true, DYN>(sv, S, point);
-        if (COUNT) { cn->march_steps++; cn->sdf_evals += n.evals; }
-        if (n.ref == omd::REF_NONE) return true;
-        if (n.d < HIT_SIZE) {
-            out.t = t; out.ref = n.ref; out.point = point;
-            out.normal = marched_normal<true, DYN>(sv, S, n.ref, point);
-            if (COUNT) cn->normal_evals++;
-            return true;
-        }
-        t += n.d;
-    }
-    return true;
-}
-
 // ============================================================================================================================
 // k_render_pool<COUNT, MA>: MA as in k_render (0 = no marched structures / dyn objects, 1 = candidate grid or distance BVH,
 // 3 = dyn marched objects).  The scene image is always staged (the host only picks this kernel when everything fits).
@@ -287,9 +244,9 @@ __global__ void __launch_bounds__(POOL_T, 1) k_render_pool(const __grid_constant
                     float mt = P.mt;
                     uint32_t mleft = P.mleft;
                     bool over;
-                    if constexpr (MA == 1) over = pool_march<COUNT, true, false>(sv, S, P.ray, A.tmin, A.tmax, P.hit_t, mt, mleft, OM_POOL_MARCH_STEPS, m, &cn);
-                    else if constexpr (MA == 3) over = pool_march<COUNT, false, true>(sv, S, P.ray, A.tmin, A.tmax, P.hit_t, mt, mleft, OM_POOL_MARCH_STEPS, m, &cn);
-                    else over = pool_march<COUNT, false, false>(sv, S, P.ray, A.tmin, A.tmax, P.hit_t, mt, mleft, OM_POOL_MARCH_STEPS, m, &cn);
+                    if constexpr (MA == 1) over = march_some<true, COUNT, true, false>(sv, S, P.ray, A.tmin, A.tmax, P.hit_t, mt, mleft, OM_POOL_MARCH_STEPS, m, &cn);
+                    else if constexpr (MA == 3) over = march_some<true, COUNT, false, true>(sv, S, P.ray, A.tmin, A.tmax, P.hit_t, mt, mleft, OM_POOL_MARCH_STEPS, m, &cn);
+                    else over = march_some<true, COUNT, false, false>(sv, S, P.ray, A.tmin, A.tmax, P.hit_t, mt, mleft, OM_POOL_MARCH_STEPS, m, &cn);
                     if (!over) {
                         still_marching = true;
                         sl[5u * POOL_N + s].w = mt;
