@@ -590,18 +590,15 @@ def test_large_bvh_equals_linear_scan(api, A, freeze_flags):
 def test_adaptive_pixels_redealt_between_handles_bit_exact(api, A, rtiow, world, rebalance):
     """dist.AdaptiveScheduler's protocol with the ranks emulated by `world` handles on one GPU: chunk owner table ->
     pass -> export owned states -> integer sum -> import everywhere -> live pixels per chunk -> next deal.  The frame and
-    the credited total must be those of one handle rendering alone."""
+    the credited total must be those of the oracle's adaptive render of the same frame."""
     import torch
     from raytracingoneweekend_b200 import dist as D
-    fz, _ = rtiow
+    fz, osc = rtiow
     W, H, spp, pass_spp = 200, 130, 40, 8
     cam = cam_rtiow(api, W / H)
     p = api.render_params(W, H, spp, seed=31, flags=A.RENDER_ADAPTIVE)
-    ref = api.Renderer(fz, cam, p)
-    for _ in range(spp // pass_spp):
-        ref.launch(pass_spp)
-    want, want_credited = ref.read_pixels(), ref.samples_done()
-    ref.close()
+    ref = osc.render(cam, p)   # the ORACLE's adaptive render (render_thread.rs:176-200), not another GPU handle
+    want, want_credited = ref["pixels"], ref["credited"]
     assert (want["n"] < spp).any() and (want["n"] == spp).any()  # some pixels retired early, some did not
     rs = [api.Renderer(fz, cam, p) for _ in range(world)]
     states = [torch.empty((W * H, 8), dtype=torch.int32, device="cuda") for _ in range(world)]
