@@ -285,14 +285,20 @@ struct Best {
 __device__ __forceinline__ void accept(Best& b, float t, uint32_t ref) {
     if (t < b.t || b.ref == omd::REF_NONE || ref > b.ref) { b.t = t; b.ref = ref; }
 }
+#ifndef OM_RARE_PRIMS_OUT_OF_LINE
+#define OM_RARE_PRIMS_OUT_OF_LINE 0  // 1: every primitive test but the sphere's is one out-of-line function (smaller hot loop; experiment)
+#endif
+// the primitive kinds that the benchmark scenes hold a handful of (cube, triangle, plane, parallelogram, dyn quadric)
 template <bool SMEM>
-__device__ __forceinline__ void test_prim(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t ref, const Ray& r, float t_min, Best& best) {
+#if OM_RARE_PRIMS_OUT_OF_LINE
+__device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+Best test_prim_other(SceneView<SMEM> sv, const SceneHeader& S, uint32_t ref, Ray r, float t_min, Best best) {
     const uint32_t type = omd::ref_type(ref), i = omd::ref_index(ref);
     float t;
-    if (type == omd::PT_SPHERE) {
-        const uint32_t u = S.off_hot[omd::PT_SPHERE] + omd::U_XF * i;
-        if (sphere_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), r, t_min, best.t, t)) accept(best, t, ref);
-    } else if (type == omd::PT_CUBE) {
+    if (type == omd::PT_CUBE) {
         const uint32_t u = S.off_hot[omd::PT_CUBE] + omd::U_XF * i;
         int axis;
         if (cube_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), r, t_min, best.t, t, axis)) accept(best, t, ref);
@@ -306,6 +312,15 @@ __device__ __forceinline__ void test_prim(const SceneView<SMEM>& sv, const Scene
         const uint32_t u = S.off_hot[type] + omd::U_BARY * i;
         if (bary_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), sv.hot(u + 3), type == omd::PT_TRI, r, t_min, best.t, t)) accept(best, t, ref);
     }
+    return best;
+}
+template <bool SMEM>
+__device__ __forceinline__ void test_prim(const SceneView<SMEM>& sv, const SceneHeader& S, uint32_t ref, const Ray& r, float t_min, Best& best) {
+    if (omd::ref_type(ref) == omd::PT_SPHERE) {
+        const uint32_t u = S.off_hot[omd::PT_SPHERE] + omd::U_XF * omd::ref_index(ref);
+        float t;
+        if (sphere_t(sv.hot(u), sv.hot(u + 1), sv.hot(u + 2), r, t_min, best.t, t)) accept(best, t, ref);
+    } else best = test_prim_other(sv, S, ref, r, t_min, best);
 }
 
 struct Counters {

@@ -30,33 +30,53 @@ def render(api, fz, cam, W, H, spp, flags=0, seed=1, passes=(0,), **kw):
     return out
 
 
+STAT_SCENES = {  # fixtures of tools/make_golden_stat.py: per-pixel mean and sample variance of n oracle samples
+    "rtiow": ("random_scene", 1, "rtiow_300x200_4096spp.npz"),      # the north_star's check: 4096 spp, at 300 x 200
+    "glass": ("glass_heavy", 4, "glass_150x100_2048spp.npz"),       # C4's scene: >= 50 % dielectric
+    "marched": ("marched", 3, "marched_96x64_1024spp.npz"),         # C3's scene: 65 marched objects
+}
+# measured on a B200 (round 2), raw = no floors at all: see the table in DESIGN.md section 2
+RAW_EXCEEDANCE_BAR = {"rtiow": 0.006, "glass": 0.008, "marched": 0.006}
+
+
 @pytest.mark.parametrize("build", ["fast", "exact"])
-def test_converged_image_within_3_sigma_of_oracle(api, A, rtiow, build):
-    """north_star: converged images at 4096 spp agree per pixel within 3 sigma of the measured per-pixel
-    sample variance; RMSE stated.  Oracle side: tests/golden/rtiow_96x64_4096spp.npz (seed 2024);
-    GPU side: an independent 4096-spp render (seed 77)."""
-    g = np.load(os.path.join(GOLD, "rtiow_96x64_4096spp.npz"))
-    n_ref = float(g["n"])
-    mu_ref = g["sum"].astype(np.float64) / n_ref
-    var = np.maximum(g["sumsq"].astype(np.float64) / n_ref - mu_ref ** 2, 0.0) * n_ref / (n_ref - 1.0)
-    px, _, traced = render(api, rtiow, cam_rtiow(api), 96, 64, 4096, flags=0 if build == "exact" else A.RENDER_FAST_MATH, seed=77)
-    assert traced == 96 * 64 * 4096 and (px["n"] == 4096).all()
-    mu = px["sum"].astype(np.float64) / 4096.0
-    # sigma of the difference of two independent means.  Two floors keep the statistic meaningful
-    # where the MEASURED variance is (near) zero although the true one is not: the rounding of the
-    # f32 running sums (Stats.sum is f32 on both sides, ~1e-5 relative), and 1/8 of one 8-bit
-    # display level (5e-4) for pixels whose rare bright paths did not occur in the 4096 oracle samples.
-    sigma = np.sqrt(var / n_ref + var / 4096.0 + (1e-5 * mu_ref) ** 2 + 5e-4 ** 2)
-    z = np.abs(mu - mu_ref) / sigma
-    raw = np.abs(mu - mu_ref) / np.maximum(np.sqrt(var / n_ref + var / 4096.0), 1e-9)
-    print("   without floors: frac(|z|>3) = %.4f" % float((raw > 3.0).mean()))
+@pytest.mark.parametrize("scene", ["rtiow", "glass", "marched"])
+def test_converged_image_within_3_sigma_of_oracle(api, A, scene, build):
+    """north_star: converged images agree per pixel within 3 sigma of the measured per-pixel sample variance; RMSE stated.
+    Oracle side: tests/golden/<scene>_*.npz (n samples per pixel, seeds 2024-2026); GPU side: an independent render with as many
+    samples and another seed, in both builds.  Two statistics:
+      raw      z = |mu_gpu - mu_ref| / sqrt(2 var_ref / n) over the pixel-channels whose MEASURED variance is not zero - no floors;
+               a Gaussian gives 0.27 % beyond 3; these are heavy-tailed Monte-Carlo estimates whose variance is itself estimated from
+               n samples, so somewhat more is expected, and the bar is what was measured plus a margin;
+      floored  the same with sigma floored by the f32 rounding of the running sums (1e-5 relative) and 1/8 of an 8-bit display level,
+               over ALL pixel-channels: this one also covers the pixels whose n oracle samples happened to be identical."""
+    kind, sseed, fname = STAT_SCENES[scene]
+    g = np.load(os.path.join(GOLD, fname))
+    n, W, H = int(g["n"]), int(g["width"]), int(g["height"])
+    mu_ref, var = g["mean"].astype(np.float64), g["var"].astype(np.float64)
+    fz = api.FrozenHittableList.generate(kind, sseed)
+    px, _, traced = render(api, fz, cam_rtiow(api, W / H), W, H, n, flags=0 if build == "exact" else A.RENDER_FAST_MATH, seed=77)
+    assert traced == W * H * n and (px["n"] == n).all()
+    mu = px["sum"].astype(np.float64) / n
+    diff = np.abs(mu - mu_ref)
+    has_var = var > 0
+    raw = diff[has_var] / np.sqrt(2.0 * var[has_var] / n)
+    raw3 = float((raw > 3.0).mean())
+    sigma = np.sqrt(2.0 * var / n + (1e-5 * mu_ref) ** 2 + 5e-4 ** 2)
+    z = diff / sigma
     frac3 = float((z > 3.0).mean())
     rmse = float(np.sqrt(np.mean((mu - mu_ref) ** 2)))
-    print("%s build: frac(|z|>3) = %.4f (0.0027 expected), max z = %.2f, RMSE = %.5f, mean = %.4f vs %.4f" % (build, frac3, z.max(), rmse, mu.mean(), mu_ref.mean()))
-    assert frac3 < 0.01          # Gaussian expectation 0.27 %; heavy-tailed pixels (glass) allowed up to 1 %
-    assert z.max() < 8.0
-    assert rmse < 0.01
+    print("%s / %s build, %dx%d, %d spp: raw frac(|z|>3) = %.4f over %.1f %% of the pixel-channels (0.0027 for a Gaussian), floored frac = %.4f, max floored z = %.2f, "
+          "RMSE = %.5f, mean = %.4f vs %.4f" % (scene, build, W, H, n, raw3, 100.0 * has_var.mean(), frac3, z.max(), rmse, mu.mean(), mu_ref.mean()))
+    assert raw3 < RAW_EXCEEDANCE_BAR[scene]
+    assert has_var.mean() > 0.9
+    assert frac3 < 0.01 and z.max() < 8.0
+    assert rmse < (0.01 if scene == "rtiow" else 0.02)
     assert abs(mu.mean() - mu_ref.mean()) < 2e-3
+    # the pixels without measured variance (every oracle sample identical, e.g. a path that always ends on the same sky colour is not one:
+    # the jitter moves it) must agree to the rounding of the f32 sums
+    if (~has_var).any():
+        assert (diff[~has_var] <= 1e-4 + 1e-4 * mu_ref[~has_var]).mean() > 0.9
 
 
 def test_fast_and_exact_builds_agree_statistically(api, A, rtiow):
