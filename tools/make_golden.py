@@ -3,8 +3,7 @@
     python tools/make_golden.py            # ~3 minutes on 8 cores
 
 Fixtures (all for the product generator's random_scene(seed=1), camera of main.rs:136-142):
-  rtiow_96x64_4096spp.npz   per-pixel sum and sum of squares of 4096 oracle samples (seed 2024): the
-                            mean and the measured sample variance of the 3-sigma image test
+  (the statistical fixtures of the 3-sigma image test come from tools/make_golden_stat.py)
   rtiow_primary_240x160.npz primary-hit (obj_id, t) maps: pixel-centre rays and sample-3 rays (seed 5)
   rtiow_exact_64x48.npz     full Stats of a 64x48, 12 spp render (seed 11), fixed and adaptive (spp 48)
 """
@@ -35,7 +34,4 @@ pa = api.render_params(64, 48, 48, seed=11, flags=A.RENDER_ADAPTIVE)
 b = osc.render(cam(64 / 48), pa)
 np.savez_compressed(os.path.join(OUT, "rtiow_exact_64x48.npz"), fixed=a["pixels"], adaptive=b["pixels"], adaptive_credited=b["credited"], adaptive_traced=b["traced"])
 print("small fixtures", time.time() - t0)
-p = api.render_params(96, 64, 4096, seed=2024)
-r = osc.render(cam(1.5), p, want_sumsq=True)
-np.savez_compressed(os.path.join(OUT, "rtiow_96x64_4096spp.npz"), sum=r["pixels"]["sum"].astype(np.float32), sumsq=r["sumsq"].astype(np.float64), n=4096, seed=2024)
 print("done", time.time() - t0)
