@@ -306,7 +306,8 @@ def run_ours(args):
         step()
     barrier()
     job.r.elapsed_ms()  # drop warm-up launch timings
-    kernels0 = job.r.perf_counters()["kernels"]
+    pc0 = job.r.perf_counters()
+    kernels0, graphs0 = pc0["kernels"], pc0["graph_launches"]
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -332,6 +333,7 @@ def run_ours(args):
     kern_ms, kern_launches = job.r.elapsed_ms()
     pcs = job.r.perf_counters()
     kernels_timed = pcs["kernels"] - kernels0
+    graphs_timed = pcs["graph_launches"] - graphs0
     wavefront = bool(pcs["flags"] & A.RENDER_WAVEFRONT)
     pool = bool(pcs["flags"] & A.RENDER_POOL)
     # samples of one step: fixed spp = every pixel x spp; adaptive = what was actually traced (rank 0 holds the whole frame)
@@ -463,6 +465,7 @@ def run_ours(args):
                        "tile_order": "the timed steps reuse the tile-cost order that the first warm-up step measured with a pilot launch of 1/64 of the samples; the e2e figure creates a fresh handle per step and pays for the pilot every time"},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 40},
             "gpu_launches": int(kernels_timed) + args.steps * (3 if (world > 1 and not args.adaptive) else 0),
+            "graph_launches": int(graphs_timed),  # of gpu_launches' kernels, how many CUDA-graph launches carried them (wavefront: 144 kernels each)
             "clocks": clocks, "roofline": roofline, "samples_traced_rank0": traced, "samples_per_step": samples_step,
         }
         if phase_ms:

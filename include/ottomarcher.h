@@ -372,7 +372,8 @@ OM_API om_status om_render_samples_traced(om_render* r, uint64_t* traced);
  * (with OM_RENDER_WAVEFRONT or OM_RENDER_PERSISTENT as chosen when the caller set neither),
  * [12] 1 if that pipeline keeps the scene image in shared memory.  Device again (OM_RENDER_COUNTERS,
  * persistent kernel): [13] path-loop iterations summed over warps, [14] the same summed over the lanes
- * that carried a path ([14] / (32 * [13]) = lane occupancy of the loop).  Synchronises.        */
+ * that carried a path ([14] / (32 * [13]) = lane occupancy of the loop).  Host: [15] CUDA graph launches among [10]'s
+ * kernels (the wavefront pipeline replays 48 iterations = 144 kernels per graph launch).  Synchronises.  */
 OM_API om_status om_render_perf_counters(om_render* r, uint64_t out[16]);
 /* device time of the launches since the last call to this function, in ms (CUDA events on the
  * render stream).  Synchronises.                                                              */

@@ -403,7 +403,7 @@ class Renderer:
     def perf_counters(self):
         v = (C.c_uint64 * 16)(); _lib.call("om_render_perf_counters", self.h, v)
         names = ["credited", "traced", "_ticket", "segments", "node_visits", "prim_tests", "sdf_evals", "march_steps", "normal_evals", "march_entered",
-                 "kernels", "flags", "scene_in_smem", "warp_iters", "lane_iters"]
+                 "kernels", "flags", "scene_in_smem", "warp_iters", "lane_iters", "graph_launches"]
         return dict(zip(names, v))
 
     def elapsed_ms(self):

@@ -270,6 +270,7 @@ struct om_render {
     float acc_ms = 0.f;
     uint32_t launches = 0;
     uint64_t kernels = 0;         // kernels launched by om_render_launch since create (om_render_perf_counters [10])
+    uint64_t graph_launches = 0;  // of which through CUDA graphs: graph launches (om_render_perf_counters [15])
     bool use_smem = false;       // k_render: scene image in shared memory (one 1024-thread CTA per SM)
     bool use_smem_hook = false;  // parity-hook kernels (two 256-thread CTAs per SM)
     size_t smem_bytes = 0;       // k_render: scene image + traversal stacks
@@ -545,6 +546,33 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     const uint32_t TIMED = 32;
     std::vector<cudaEvent_t> tev;
     if (timing) { tev.resize(4 * TIMED); for (auto& ev : tev) CU(cudaEventCreate(&ev)); }
+    // The kernels use the iteration index only as it % 3 (counter set) and it & 1 (queue parity), so a run of iterations whose length
+    // is a multiple of 6 has the same arguments wherever it starts: GRAPH_ITERS iterations are captured ONCE per call into a CUDA graph
+    // and replayed - 144 kernels per launch instead of one (C5: 6339 launches per frame -> 45).  Iterations past the end of the frame
+    // find empty queues and return at once.  OM_WF_NO_GRAPH=1 (or the timing mode) keeps the kernel-by-kernel loop.
+    const uint32_t GRAPH_ITERS = 48;
+    cudaGraphExec_t graph_exec = nullptr;
+    if (!timing && !getenv("OM_WF_NO_GRAPH")) {
+        cudaGraph_t graph = nullptr;
+        e = cudaStreamBeginCapture(r->stream, cudaStreamCaptureModeThreadLocal);
+        if (e == cudaSuccess) {
+            for (uint32_t k = 0; k < GRAPH_ITERS && e == cudaSuccess; k++) {
+                w.it = k;
+                e = exact ? om_exact::launch_wf_extend(a, w, r->wf_smem, count, r->wf_grid_extend, smem, r->stream)
+                          : om_fast::launch_wf_extend(a, w, r->wf_smem, count, r->wf_grid_extend, smem, r->stream);
+                if (e == cudaSuccess) e = exact ? om_exact::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream) : om_fast::launch_wf_shade(a, w, count, r->wf_grid_small, r->stream);
+                if (e == cudaSuccess) e = om_exact::launch_wf_compact(w, r->wf_grid_small, r->stream);
+            }
+            const cudaError_t e2 = cudaStreamEndCapture(r->stream, &graph);
+            if (e == cudaSuccess) e = e2;
+        }
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&graph_exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (e != cudaSuccess) {  // (an unsupported capture is not an error of the render: fall back to plain launches)
+            cudaGetLastError();
+            graph_exec = nullptr;
+        }
+    }
     uint32_t it = 0;
     bool pending[2] = {false, false};
     uint32_t it_at[2] = {0, 0};
@@ -559,6 +587,13 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
             for (int c = 0; c < omk::wf::N_CLS; c++) live += hs[omk::wf::C_N_SHADE + omk::wf::C_STRIDE * c];
             if (live < TAIL) break;
         }
+        if (graph_exec) {  // one launch = GRAPH_ITERS iterations (their arguments only depend on it % 6, see above)
+            e = cudaGraphLaunch(graph_exec, r->stream);
+            if (e != cudaSuccess) { cudaGraphExecDestroy(graph_exec); return fail(OM_ERR_CUDA, "wavefront graph launch failed: %s", cudaGetErrorString(e)); }
+            it += GRAPH_ITERS;
+            r->kernels += 3 * GRAPH_ITERS;
+            r->graph_launches++;
+        } else
         for (uint32_t k = 0; k < BATCH; k++, it++) {
             w.it = it;
             if (timing && it >= 8 && it < 8 + TIMED) CU(cudaEventRecord(tev[4 * (it - 8)], r->stream));
@@ -581,6 +616,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     }
     for (int i = 0; i < 2; i++)
         if (pending[i]) { CU(cudaEventSynchronize(r->wf_ev[i])); }
+    if (graph_exec) { CU(cudaStreamSynchronize(r->stream)); cudaGraphExecDestroy(graph_exec); }
     if (timing && it >= 8 + TIMED) {
         CU(cudaStreamSynchronize(r->stream));
         float t_ext = 0, t_sh = 0, t_co = 0, t_gap = 0;
@@ -733,6 +769,7 @@ om_status om_render_perf_counters(om_render* r, uint64_t out[16]) {
     out[10] = r->kernels;
     out[11] = r->p.flags;  // with the pipeline that was chosen when the caller left it open
     out[12] = (r->p.flags & OM_RENDER_WAVEFRONT) ? (r->wf_smem ? 1 : 0) : (r->use_smem ? 1 : 0);
+    out[15] = r->graph_launches;
     return OM_OK;
 }
 om_status om_render_elapsed_ms(om_render* r, float* ms, uint32_t* launches) {
