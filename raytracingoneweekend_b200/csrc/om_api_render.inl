@@ -551,7 +551,13 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     // and replayed - 144 kernels per launch instead of one (C5: 6339 launches per frame -> 45).  Iterations past the end of the frame
     // find empty queues and return at once.  OM_WF_NO_GRAPH=1 (or the timing mode) keeps the kernel-by-kernel loop.
     const uint32_t GRAPH_ITERS = 48;
-    cudaGraphExec_t graph_exec = nullptr;
+    struct GraphOwner {  // destroyed on every way out of this function, after the work it has in flight
+        cudaGraphExec_t exec = nullptr;
+        cudaStream_t stream = nullptr;
+        ~GraphOwner() { if (exec) { cudaStreamSynchronize(stream); cudaGraphExecDestroy(exec); } }
+    } graph_owner;
+    graph_owner.stream = r->stream;
+    cudaGraphExec_t& graph_exec = graph_owner.exec;
     if (!timing && !getenv("OM_WF_NO_GRAPH")) {
         cudaGraph_t graph = nullptr;
         e = cudaStreamBeginCapture(r->stream, cudaStreamCaptureModeThreadLocal);
@@ -589,7 +595,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
         }
         if (graph_exec) {  // one launch = GRAPH_ITERS iterations (their arguments only depend on it % 6, see above)
             e = cudaGraphLaunch(graph_exec, r->stream);
-            if (e != cudaSuccess) { cudaGraphExecDestroy(graph_exec); return fail(OM_ERR_CUDA, "wavefront graph launch failed: %s", cudaGetErrorString(e)); }
+            if (e != cudaSuccess) return fail(OM_ERR_CUDA, "wavefront graph launch failed: %s", cudaGetErrorString(e));
             it += GRAPH_ITERS;
             r->kernels += 3 * GRAPH_ITERS;
             r->graph_launches++;
@@ -616,7 +622,7 @@ om_status run_wavefront(om_render* r, omk::RenderArgs& a, uint32_t n_target) {
     }
     for (int i = 0; i < 2; i++)
         if (pending[i]) { CU(cudaEventSynchronize(r->wf_ev[i])); }
-    if (graph_exec) { CU(cudaStreamSynchronize(r->stream)); cudaGraphExecDestroy(graph_exec); }
+    if (graph_exec) { CU(cudaStreamSynchronize(r->stream)); cudaGraphExecDestroy(graph_exec); graph_exec = nullptr; }
     if (timing && it >= 8 + TIMED) {
         CU(cudaStreamSynchronize(r->stream));
         float t_ext = 0, t_sh = 0, t_co = 0, t_gap = 0;

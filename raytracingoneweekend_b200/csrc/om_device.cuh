@@ -709,11 +709,20 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
             const float4 cc = sv.cold(S.off_mgrid_cells + (cell >> 1));
             const uint32_t first = __float_as_uint((cell & 1u) ? cc.z : cc.x), count = __float_as_uint((cell & 1u) ? cc.w : cc.y);
             n.evals = count;
-            for (uint32_t k = first; k < first + count; k++) {
-                const uint32_t ref = marched_ref<false>(S, word(S.off_mgrid_lists, k));
-                const float d = fabsf(marched_sdf<SMEM, false>(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
-                if (d < n.d) { n.d = d; n.ref = ref; }
-            }
+            // A list holds indices of the reference's scan in increasing order, i.e. spheres, then boxes, then tori.  One loop per
+            // type: the lanes of a warp have lists of different make-up, and a single loop with the type switch inside ran
+            // all three bodies in most of its trips (4.2 lanes per instruction in the SDFs, ncu of C3).
+            const uint32_t end = first + count, n_ms = S.n[omd::PT_MSPHERE], n_sb = n_ms + S.n[omd::PT_MBOX];
+            uint32_t k = first, j = k < end ? word(S.off_mgrid_lists, k) : 0xFFFFFFFFu;
+            auto take = [&](uint32_t type, uint32_t i) {
+                const float d = fabsf(marched_sdf<SMEM, false>(sv, S, type, i, p));
+                if (d < n.d) { n.d = d; n.ref = omd::make_ref(type, i); }
+                k++;
+                j = k < end ? word(S.off_mgrid_lists, k) : 0xFFFFFFFFu;
+            };
+            while (j < n_ms) take(omd::PT_MSPHERE, j);
+            while (j < n_sb) take(omd::PT_MBOX, j - n_ms);
+            while (j != 0xFFFFFFFFu) take(omd::PT_MTORUS, j - n_sb);
             return n;
         }
     }
