@@ -136,6 +136,7 @@ struct SceneView {
         return __ldg(hot_g + u);
     }
     __device__ __forceinline__ float4 cold(uint32_t u) const { return __ldg(cold_g + u); }
+    __device__ __forceinline__ uint32_t cold_word(uint32_t u, uint32_t i) const { return __ldg(reinterpret_cast<const uint32_t*>(cold_g + u) + i); }
     __device__ __forceinline__ uint32_t hot_word(uint32_t u, uint32_t i) const {  // 32-bit word i of the section starting at unit u
         if (SMEM) return reinterpret_cast<const uint32_t*>(om_smem + u)[i];
         return __ldg(reinterpret_cast<const uint32_t*>(hot_g + u) + i);
@@ -445,6 +446,18 @@ __device__ __forceinline__ bool visit4(const SceneView<SMEM>& sv, const SceneHea
     const float4 ny = sv.hot(u + 2u + sy), fy = sv.hot(u + 2u + (sy ^ 1u));
     const float4 nz = sv.hot(u + 4u + sz), fz = sv.hot(u + 4u + (sz ^ 1u));
     const float4 cf = sv.hot(u + 6u);
+    // per-ray padding (global-memory variant): ONE margin per node, from the farthest point of its children's boxes - at least the
+    // margin each child would get from its own box (the padding only ever has to be large enough), and one square root instead of four
+    float ex = 0.f, ey = 0.f, ez = 0.f;
+    if (!SMEM && pad != 0.f) {
+        auto far4 = [&](float4 n, float4 f, float o1) {  // an empty slot's planes are (+INF, -INF) or the reverse: no part in the maximum
+            auto one = [&](float a, float b) { return (fabsf(a) < kInf && fabsf(b) < kInf) ? fmaxf(fabsf(a - o1), fabsf(b - o1)) : 0.f; };
+            return fmaxf(fmaxf(one(n.x, f.x), one(n.y, f.y)), fmaxf(one(n.z, f.z), one(n.w, f.w)));
+        };
+        const float dx = far4(nx, fx, o.x), dy = far4(ny, fy, o.y), dz = far4(nz, fz, o.z);
+        const float e = pad * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+        ex = e * fabsf(q.inv.x); ey = e * fabsf(q.inv.y); ez = e * fabsf(q.inv.z);
+    }
     auto key = [&](float nxj, float fxj, float nyj, float fyj, float nzj, float fzj, uint32_t j) -> uint32_t {
         float ax = fmaf(nxj, q.inv.x, q.noinv.x), bx = fmaf(fxj, q.inv.x, q.noinv.x);
         float ay = fmaf(nyj, q.inv.y, q.noinv.y), by = fmaf(fyj, q.inv.y, q.noinv.y);
@@ -452,9 +465,6 @@ __device__ __forceinline__ bool visit4(const SceneView<SMEM>& sv, const SceneHea
         bool real = true;
         if (!SMEM && pad != 0.f) {
             real = ax <= bx;  // an empty slot's inverted box (+INF, -INF) would pad to NaN planes, which fmaxf / fminf drop
-            const float dx = fmaxf(fabsf(nxj - o.x), fabsf(fxj - o.x)), dy = fmaxf(fabsf(nyj - o.y), fabsf(fyj - o.y)), dz = fmaxf(fabsf(nzj - o.z), fabsf(fzj - o.z));
-            const float e = pad * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
-            const float ex = e * fabsf(q.inv.x), ey = e * fabsf(q.inv.y), ez = e * fabsf(q.inv.z);
             ax -= ex; bx += ex; ay -= ey; by += ey; az -= ez; bz += ez;
         }
         const float tn = fmaxf(fmaxf(ax, ay), fmaxf(az, t_min));
@@ -697,11 +707,7 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
     n.d = kInf;
     n.ref = omd::REF_NONE;
     n.evals = 0;
-    auto word = [&](uint32_t off, uint32_t i) {
-        const float4 l4 = sv.cold(off + (i >> 2));
-        const uint32_t sel = i & 3u;
-        return __float_as_uint(sel == 0u ? l4.x : (sel == 1u ? l4.y : (sel == 2u ? l4.z : l4.w)));
-    };
+    auto word = [&](uint32_t off, uint32_t i) { return sv.cold_word(off, i); };
     if (S.mgrid_dim[0] != 0u) {
         const float fx = (p.x - S.mgrid_lo[0]) * S.mgrid_inv_h, fy = (p.y - S.mgrid_lo[1]) * S.mgrid_inv_h, fz = (p.z - S.mgrid_lo[2]) * S.mgrid_inv_h;
         if (fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < (float)S.mgrid_dim[0] && fy < (float)S.mgrid_dim[1] && fz < (float)S.mgrid_dim[2]) {
@@ -727,14 +733,20 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
         }
     }
     bool walk = S.n_mbvh_nodes != 0u;
+    // A subtree is skipped when mbvh_f * dist(p, box) - slack > n.d.  The walk compares SQUARED distances with the squared
+    // threshold instead (two IEEE square roots per node were a third of its instructions); the threshold is widened by 1e-5
+    // relative, far more than the round-off of either side, so the squared test never skips what the plain one keeps.
     const float slack = S.mbvh_margin + 1e-5f * (fabsf(p.x) + fabsf(p.y) + fabsf(p.z));
-    auto lower = [&](float lx, float ly, float lz, float hx, float hy, float hz) {
+    const float inv_f = 1.f / S.mbvh_f;
+    auto lower2 = [&](float lx, float ly, float lz, float hx, float hy, float hz) {
         const float dx = fmaxf(fmaxf(lx - p.x, p.x - hx), 0.f), dy = fmaxf(fmaxf(ly - p.y, p.y - hy), 0.f), dz = fmaxf(fmaxf(lz - p.z, p.z - hz), 0.f);
-        return S.mbvh_f * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - slack;
+        return fmaf(dx, dx, fmaf(dy, dy, dz * dz));
     };
+    auto reach2 = [&](float d) { const float r = (d + slack) * inv_f; return r * r * 1.00001f; };  // (+INF stays +INF)
+    float lim2 = reach2(n.d);
     uint32_t k = 0, best_j = 0xFFFFFFFFu;
     int sp = 1;
-    stk[0] = make_int2(0, __float_as_int(-1.f));  // the root, after the scene-sized objects of the always list
+    stk[0] = make_int2(0, __float_as_int(0.f));  // the root, after the scene-sized objects of the always list
     while (walk) {
         uint32_t j = 0xFFFFFFFFu;
         if (k < S.n_mbvh_always) { j = word(S.off_mbvh_always, k); k++; }
@@ -742,16 +754,16 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
             while (sp > 0) {
                 sp--;
                 const int2 e = stk[sp];
-                if (__int_as_float(e.y) > n.d) continue;
+                if (__int_as_float(e.y) > lim2) continue;
                 if (e.x < 0) { j = (uint32_t)(~e.x); break; }
                 const uint32_t u = S.off_mbvh_nodes + omd::U_NODE * (uint32_t)e.x;
                 const float4 n0 = sv.cold(u), n1 = sv.cold(u + 1), n2 = sv.cold(u + 2), n3 = sv.cold(u + 3);
-                float dl = lower(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y), dr = lower(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w);
+                float dl = lower2(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y), dr = lower2(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w);
                 int cl = __float_as_int(n3.x), cr = __float_as_int(n3.y);
                 if (dr < dl) { const float t = dl; dl = dr; dr = t; const int c = cl; cl = cr; cr = c; }  // (cl, dl): the nearer child, popped first
                 if (sp + 2 > MSTACK) { walk = false; break; }
-                if (!(dr > n.d)) { stk[sp] = make_int2(cr, __float_as_int(dr)); sp++; }
-                if (!(dl > n.d)) { stk[sp] = make_int2(cl, __float_as_int(dl)); sp++; }
+                if (!(dr > lim2)) { stk[sp] = make_int2(cr, __float_as_int(dr)); sp++; }
+                if (!(dl > lim2)) { stk[sp] = make_int2(cl, __float_as_int(dl)); sp++; }
             }
         }
         if (!walk) break;
@@ -759,7 +771,7 @@ __device__ __noinline__ Near nearest_marched_accel(SceneView<SMEM> sv, const Sce
         const uint32_t ref = marched_ref<false>(S, j);
         const float d = fabsf(marched_sdf<SMEM, false>(sv, S, omd::ref_type(ref), omd::ref_index(ref), p));
         n.evals++;
-        if (d < n.d || (d == n.d && j < best_j && best_j != 0xFFFFFFFFu)) { n.d = d; n.ref = ref; best_j = j; }
+        if (d < n.d || (d == n.d && j < best_j && best_j != 0xFFFFFFFFu)) { n.d = d; n.ref = ref; best_j = j; lim2 = reach2(d); }
     }
     return nearest_marched<SMEM, false>(sv, S, p);
 }
