@@ -451,8 +451,8 @@ __device__ __forceinline__ bool visit4(const SceneView<SMEM>& sv, const SceneHea
     float ex = 0.f, ey = 0.f, ez = 0.f;
     if (!SMEM && pad != 0.f) {
         auto far4 = [&](float4 n, float4 f, float o1) {  // an empty slot's planes are (+INF, -INF) or the reverse: no part in the maximum
-            auto one = [&](float a, float b) { return (fabsf(a) < kInf && fabsf(b) < kInf) ? fmaxf(fabsf(a - o1), fabsf(b - o1)) : 0.f; };
-            return fmaxf(fmaxf(one(n.x, f.x), one(n.y, f.y)), fmaxf(one(n.z, f.z), one(n.w, f.w)));
+            auto one = [&](float a, float b) { const float v = fmaxf(fabsf(a - o1), fabsf(b - o1)); return v < kInf ? v : 0.f; };
+            return fmaxf(fmaxf(fmaxf(fabsf(n.x - o1), fabsf(f.x - o1)), one(n.y, f.y)), fmaxf(one(n.z, f.z), one(n.w, f.w)));  // (slot 0 is never empty)
         };
         const float dx = far4(nx, fx, o.x), dy = far4(ny, fy, o.y), dz = far4(nz, fz, o.z);
         const float e = pad * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
