@@ -73,6 +73,9 @@ struct SceneHeader {
     // != 0: the BVH boxes carry only the distance-independent padding; the traversal widens each box by
     // dyn_pad * (largest distance from the ray origin to a point of the box), see om_scene.cpp
     float dyn_pad;
+    // with dyn_pad: one float4 per wide node at off_node_far in the hot image, {centre, radius} of a ball around the node's
+    // children - |origin - centre| + radius bounds the distance from a ray origin to any point of their boxes
+    uint32_t off_node_far;
     // dyn marched object i (PT_MDYN): world->local rows 0-2, local->world rows 0-2, {world_f, first word, word count, 0};
     // the programs' words, 4 per unit, start at off_dyn_code
     uint32_t off_dyn_code;

@@ -446,16 +446,15 @@ __device__ __forceinline__ bool visit4(const SceneView<SMEM>& sv, const SceneHea
     const float4 ny = sv.hot(u + 2u + sy), fy = sv.hot(u + 2u + (sy ^ 1u));
     const float4 nz = sv.hot(u + 4u + sz), fz = sv.hot(u + 4u + (sz ^ 1u));
     const float4 cf = sv.hot(u + 6u);
-    // per-ray padding (global-memory variant): ONE margin per node, from the farthest point of its children's boxes - at least the
-    // margin each child would get from its own box (the padding only ever has to be large enough), and one square root instead of four
+    // per-ray padding (global-memory variant): ONE margin per node, from a ball around its children's boxes that the host
+    // packed (SceneHeader::off_node_far): |o - centre| + radius is at least the distance to the farthest point of any child's
+    // box, which is what each child's own margin would use (the padding only ever has to be large enough) - one square
+    // root and a dozen instructions instead of four roots and fifty
     float ex = 0.f, ey = 0.f, ez = 0.f;
     if (!SMEM && pad != 0.f) {
-        auto far4 = [&](float4 n, float4 f, float o1) {  // an empty slot's planes are (+INF, -INF) or the reverse: no part in the maximum
-            auto one = [&](float a, float b) { const float v = fmaxf(fabsf(a - o1), fabsf(b - o1)); return v < kInf ? v : 0.f; };
-            return fmaxf(fmaxf(fmaxf(fabsf(n.x - o1), fabsf(f.x - o1)), one(n.y, f.y)), fmaxf(one(n.z, f.z), one(n.w, f.w)));  // (slot 0 is never empty)
-        };
-        const float dx = far4(nx, fx, o.x), dy = far4(ny, fy, o.y), dz = far4(nz, fz, o.z);
-        const float e = pad * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+        const float4 cr = sv.hot(S.off_node_far + node);
+        const float dx = cr.x - o.x, dy = cr.y - o.y, dz = cr.z - o.z;
+        const float e = pad * (sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + cr.w);
         ex = e * fabsf(q.inv.x); ey = e * fabsf(q.inv.y); ez = e * fabsf(q.inv.z);
     }
     auto key = [&](float nxj, float fxj, float nyj, float fyj, float nzj, float fzj, uint32_t j) -> uint32_t {

@@ -487,6 +487,23 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
         hot.f4(nd.loz[0], nd.loz[1], nd.loz[2], nd.loz[3]); hot.f4(nd.hiz[0], nd.hiz[1], nd.hiz[2], nd.hiz[3]);
         hot.u4(uint32_t(nd.child[0]), uint32_t(nd.child[1]), uint32_t(nd.child[2]), uint32_t(nd.child[3]));
     }
+    h.off_node_far = hot.units();
+    if (h.dyn_pad != 0.f) {
+        for (const omb::Node4& nd : wide.nodes) {
+            double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+            for (int j = 0; j < 4; j++) {
+                if (!(nd.lox[j] <= nd.hix[j])) continue;  // empty slot
+                lo[0] = std::min(lo[0], double(nd.lox[j])); hi[0] = std::max(hi[0], double(nd.hix[j]));
+                lo[1] = std::min(lo[1], double(nd.loy[j])); hi[1] = std::max(hi[1], double(nd.hiy[j]));
+                lo[2] = std::min(lo[2], double(nd.loz[j])); hi[2] = std::max(hi[2], double(nd.hiz[j]));
+            }
+            if (!(lo[0] <= hi[0])) { hot.f4(0.f, 0.f, 0.f, 0.f); continue; }
+            const float c[3] = {float(0.5 * (lo[0] + hi[0])), float(0.5 * (lo[1] + hi[1])), float(0.5 * (lo[2] + hi[2]))};
+            double r2 = 0;  // from the ROUNDED centre to the farthest corner
+            for (int a = 0; a < 3; a++) { const double d = std::max(std::fabs(lo[a] - double(c[a])), std::fabs(hi[a] - double(c[a]))); r2 += d * d; }
+            hot.f4(c[0], c[1], c[2], std::nextafter(float(std::sqrt(r2) * (1.0 + 1e-6)), std::numeric_limits<float>::infinity()));
+        }
+    }
     h.off_hot[PT_SPHERE] = hot.units();
     for (const om_sphere& s : L.spheres) hot.rows3(s.m_world_to_local);
     h.off_hot[PT_CUBE] = hot.units();
