@@ -457,18 +457,16 @@ __device__ __forceinline__ bool visit4(const SceneView<SMEM>& sv, const SceneHea
         const float e = pad * (sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + cr.w);
         ex = e * fabsf(q.inv.x); ey = e * fabsf(q.inv.y); ez = e * fabsf(q.inv.z);
     }
+    // the margin rides in the constant term of the planes' fma: near planes move by -e, far planes by +e
+    const float lox = q.noinv.x - ex, hix = q.noinv.x + ex, loy = q.noinv.y - ey, hiy = q.noinv.y + ey, loz = q.noinv.z - ez, hiz = q.noinv.z + ez;
     auto key = [&](float nxj, float fxj, float nyj, float fyj, float nzj, float fzj, uint32_t j) -> uint32_t {
-        float ax = fmaf(nxj, q.inv.x, q.noinv.x), bx = fmaf(fxj, q.inv.x, q.noinv.x);
-        float ay = fmaf(nyj, q.inv.y, q.noinv.y), by = fmaf(fyj, q.inv.y, q.noinv.y);
-        float az = fmaf(nzj, q.inv.z, q.noinv.z), bz = fmaf(fzj, q.inv.z, q.noinv.z);
-        bool real = true;
-        if (!SMEM && pad != 0.f) {
-            real = ax <= bx;  // an empty slot's inverted box (+INF, -INF) would pad to NaN planes, which fmaxf / fminf drop
-            ax -= ex; bx += ex; ay -= ey; by += ey; az -= ez; bz += ez;
-        }
+        const float ax = fmaf(nxj, q.inv.x, lox), bx = fmaf(fxj, q.inv.x, hix);
+        const float ay = fmaf(nyj, q.inv.y, loy), by = fmaf(fyj, q.inv.y, hiy);
+        const float az = fmaf(nzj, q.inv.z, loz), bz = fmaf(fzj, q.inv.z, hiz);
+        // (an empty slot's inverted box (+INF, -INF) gives ax = +INF or bx = -INF whatever the margin: tn <= tf fails)
         const float tn = fmaxf(fmaxf(ax, ay), fmaxf(az, t_min));
         const float tf = fminf(fminf(bx, by), fminf(bz, best_t));
-        return (real && tn <= tf) ? ((__float_as_uint(fmaxf(tn, 0.f)) & 0xFFFFFFFCu) | j) : 0xFFFFFFFFu;
+        return (tn <= tf) ? ((__float_as_uint(fmaxf(tn, 0.f)) & 0xFFFFFFFCu) | j) : 0xFFFFFFFFu;
     };
     uint32_t k0 = key(nx.x, fx.x, ny.x, fy.x, nz.x, fz.x, 0u), k1 = key(nx.y, fx.y, ny.y, fy.y, nz.y, fz.y, 1u);
     uint32_t k2 = key(nx.z, fx.z, ny.z, fy.z, nz.z, fz.z, 2u), k3 = key(nx.w, fx.w, ny.w, fy.w, nz.w, fz.w, 3u);
