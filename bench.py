@@ -437,7 +437,7 @@ def run_ours(args):
             roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6550.4",
                         "bytes_per_sample": bps, "note": "bytes the traversal asks for (112 B per node visit, 48 B per sphere test, 80 B per hit, 64 B framebuffer per pixel); "
-                                                         "the 180 MB scene image is mostly served by the 126 MB L2, so DRAM traffic is lower than this"}
+                                                         "the 16-byte bounding ball a visit also reads in scenes with per-ray box padding is not counted; the 180 MB scene image is mostly served by the 126 MB L2, so DRAM traffic is lower than this"}
         roofline.update({"traffic": traffic, "traffic_source": (ncu or {}).get("dram_bytes", {}).get("source") if traffic else None, "kernel": kernel,
                          "launch_ms": launch_ms, "per_sample": per_sample,
                          "accumulate_hbm": {"bytes_per_launch": 64 * W * H, "note": "32 B read + 32 B write per pixel per launch"},
