@@ -28,7 +28,8 @@ WANT = {
     "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio": "stall_short_scoreboard_per_issue",
     "launch__registers_per_thread": "registers_per_thread",
 }
-UNIT_SCALE = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0, "msecond": 1.0, "usecond": 1e-3, "second": 1e3, "nsecond": 1e-6}
+UNIT_SCALE = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0, "msecond": 1.0, "usecond": 1e-3, "second": 1e3, "nsecond": 1e-6,
+              "ms": 1.0, "us": 1e-3, "s": 1e3, "ns": 1e-6}
 
 
 def raw_rows(rep, kernel):
