@@ -28,6 +28,9 @@ namespace wfk {
 using namespace omk::wf;
 }
 
+#ifndef OM_WF_EXT_MIN_CTAS
+#define OM_WF_EXT_MIN_CTAS 2  // CTAs per SM the extend kernel is compiled for (64 registers at 2)
+#endif
 constexpr int WF_EXT_THREADS = 512;
 constexpr int WF_THREADS = 256;
 constexpr uint32_t WF_DESTS = (uint32_t)omk::wf::N_CLS + 1u;                 // shade classes + the march queue
@@ -66,7 +69,7 @@ __device__ __forceinline__ void wf_push(const omk::WfArgs& W, uint32_t* set, uin
 // k_wf_extend
 // ---------------------------------------------------------------------------------------------
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(WF_EXT_THREADS, 2) k_wf_extend(const __grid_constant__ RenderArgs A, const __grid_constant__ omk::WfArgs W) {
+__global__ void __launch_bounds__(WF_EXT_THREADS, OM_WF_EXT_MIN_CTAS) k_wf_extend(const __grid_constant__ RenderArgs A, const __grid_constant__ omk::WfArgs W) {
     uint32_t* cs = wf_set(W, W.it);
     const uint32_t n_ray = cs[wfk::C_N_RAY];
     if (n_ray == 0u) return;
