@@ -107,6 +107,30 @@ def test_hit_bit_exact_all_primitive_types(api, A, mixed, extra):
     assert types >= {0, 1, 2, 3, 4, 5, 6, 7, 8}, types  # every type (and the sky) was actually hit
 
 
+def test_hit_and_render_bit_exact_with_forced_ray_padding(api, A, O):
+    """OM_FREEZE_RAY_PADDING on a scene with every primitive type: the scene stays in global memory and every node visit widens
+    the child boxes by the margin of the node's bounding ball (SceneHeader::off_node_far).  Padding only decides what gets
+    tested, so hits and a render must still equal the oracle's, bit for bit, from near and from far origins."""
+    fz = build_mixed_scene(api).freeze(flags=A.FREEZE_RAY_PADDING)
+    st = fz.stats()
+    assert st["ray_padding"] == 1 and st["fits_smem"] == 0
+    osc = oracle_scene_from(O, fz)
+    rng = np.random.default_rng(13)
+    o = rng.uniform(-6, 6, (30000, 3)).astype(np.float32); o[:, 1] = rng.uniform(-0.4, 3, 30000)
+    d = rng.normal(0, 1, (30000, 3)).astype(np.float32)
+    ref = osc.trace_rays(o, d)
+    assert_hits_equal(fz.hit(o, d, flags=0), ref)
+    assert set((ref[0] >> np.uint64(32)).tolist()) >= {0, 1, 2, 3, 4, 5}
+    far = (rng.normal(0, 1, (8000, 3)) * 400).astype(np.float32)  # origins hundreds of units away, aimed at the scene
+    tgt = rng.uniform(-5, 5, (8000, 3)).astype(np.float32); tgt[:, 1] = rng.uniform(0, 2, 8000)
+    assert_hits_equal(fz.hit(far, tgt - far, 0.001, 5000.0, flags=0), osc.trace_rays(far, tgt - far, 0.001, 5000.0))
+    cam = api.Camera.new((6, 3, 7), (0, 0.5, 0), (0, 1, 0), 40.0, 1.5, 0.05, 9.0)
+    p = api.render_params(48, 32, 3, seed=5, flags=0)
+    r = api.Renderer(fz, cam, p); r.launch(0); r.sync()
+    assert_pixels_equal(r.read_pixels(), osc.render(cam, p)["pixels"])
+    r.close()
+
+
 def test_hit_edge_cases(api, A, mixed, O):
     fz, osc = mixed
     ids, t, p, n = fz.hit(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32), flags=0)
