@@ -95,6 +95,13 @@ int wf_extend_occupancy(bool smem, bool count, size_t scene_bytes) {
         if (count) { prep(k_wf_extend<true, true>, total); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<true, true>, WF_EXT_THREADS, total); }
         else { prep(k_wf_extend<true, false>, total); e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<true, false>, WF_EXT_THREADS, total); }
     } else {
+        // the scene is walked through L1 / L2: ask for the smallest shared-memory carve-out that holds the staging lines of the resident
+        // CTAs, the rest of the 256 KB goes to L1 (the kernel waits on node fetches: profiles/r2_experiments.md section 8)
+        const int carve = getenv("OM_WF_NO_CARVEOUT") ? -1 : int((size_t(OM_WF_EXT_MIN_CTAS) * (total + 1024u) * 100u + 228u * 1024u - 1u) / (228u * 1024u));
+        if (carve >= 0) {
+            cudaFuncSetAttribute(k_wf_extend<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_wf_extend<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        }
         if (count) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<false, true>, WF_EXT_THREADS, total);
         else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wf_extend<false, false>, WF_EXT_THREADS, total);
     }
