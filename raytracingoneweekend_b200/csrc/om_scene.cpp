@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <chrono>
 #include <limits>
+#include <thread>
 
 #include "om_bvh.h"
 
@@ -122,21 +123,38 @@ double half_area(const Aabb& b) {
     return dx * dy + dy * dz + dz * dx;
 }
 
+// Scenes of 1e5 objects and more: the per-object loops of freeze() run on the host's threads (every iteration writes its own
+// slots, so the images are byte-identical to the sequential ones).
+template <class F>
+void parallel_for(size_t n, F&& body) {
+    const size_t hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    if (n < 65536 || hw < 2 || getenv("OM_FREEZE_SERIAL")) { for (size_t i = 0; i < n; i++) body(i); return; }
+    std::vector<std::thread> th;
+    const size_t chunk = (n + hw - 1) / hw;
+    for (size_t t = 0; t < hw; t++) {
+        const size_t a = t * chunk, b = std::min(n, a + chunk);
+        if (a >= b) break;
+        th.emplace_back([=, &body]() { for (size_t i = a; i < b; i++) body(i); });
+    }
+    for (auto& x : th) x.join();
+}
+
 struct Packer {
     std::vector<float>& v;
     explicit Packer(std::vector<float>& v_) : v(v_) {}
     uint32_t units() const { return uint32_t(v.size() / 4); }
-    void f4(float a, float b, float c, float d) { v.push_back(a); v.push_back(b); v.push_back(c); v.push_back(d); }
+    float* grow(size_t n_units) { const size_t at = v.size(); v.resize(at + 4 * n_units); return v.data() + at; }  // (valid until the next growth)
+    void f4(float a, float b, float c, float d) { const float x[4] = {a, b, c, d}; v.insert(v.end(), x, x + 4); }
     void rows3(const float* m) { for (int r = 0; r < 3; r++) f4(m[4 * r], m[4 * r + 1], m[4 * r + 2], m[4 * r + 3]); }
     void u4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) { float f[4]; uint32_t u[4] = {a, b, c, d}; memcpy(f, u, 16); f4(f[0], f[1], f[2], f[3]); }
 };
 float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
-void pack_material(Packer& p, const om_material& m, uint32_t pt, size_t index) {
+void pack_material(float* dst, const om_material& m, uint32_t pt, size_t index) {  // two units
     const uint64_t id = OM_OBJ_ID(pt + 1, index);  // ABI type tag = scan-order code + 1
     const uint64_t bloom = omh::bloom_get_hash(id);
-    p.f4(m.albedo[0], m.albedo[1], m.albedo[2], m.fuzz);
-    p.f4(m.ior, u2f(m.mat_type), u2f(uint32_t(bloom)), u2f(uint32_t(bloom >> 32)));
+    const float x[8] = {m.albedo[0], m.albedo[1], m.albedo[2], m.fuzz, m.ior, u2f(m.mat_type), u2f(uint32_t(bloom)), u2f(uint32_t(bloom >> 32))};
+    memcpy(dst, x, sizeof x);
 }
 
 // ---- candidate grid over the marched objects (see SceneHeader::mgrid_*) -------------------------------------
@@ -390,8 +408,8 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
             const double p[3] = {x, y, z};
             for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a] - r); hi[a] = std::max(hi[a], p[a] + r); }
         };
-        std::vector<double> radii;
-        for (const om_sphere& o : L.spheres) radii.push_back(col_norm_min(o.m_local_to_world));
+        std::vector<double> radii(L.spheres.size());
+        parallel_for(L.spheres.size(), [&](size_t i) { radii[i] = col_norm_min(L.spheres[i].m_local_to_world); });
         double med = 0.0;
         if (!radii.empty()) { std::vector<double> t = radii; std::nth_element(t.begin(), t.begin() + t.size() / 2, t.end()); med = t[t.size() / 2]; }
         for (size_t i = 0; i < L.spheres.size(); i++)
@@ -411,8 +429,8 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     // let the traversal add it per ray (SceneHeader::dyn_pad).
     bool dyn = (flags & 2u) != 0;
     if (!(flags & 6u) && L.spheres.size() >= 64) {
-        std::vector<double> fat;
-        for (const om_sphere& o : L.spheres) fat.push_back(sphere_fat(o, reach));
+        std::vector<double> fat(L.spheres.size());
+        parallel_for(L.spheres.size(), [&](size_t i) { fat[i] = sphere_fat(L.spheres[i], reach); });
         std::nth_element(fat.begin(), fat.begin() + fat.size() / 2, fat.end());
         dyn = fat[fat.size() / 2] > 0.5;
     }
@@ -430,7 +448,9 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     std::vector<Aabb> boxes;
     refs.reserve(L.spheres.size() + L.cubes.size() + L.triangles.size() + L.parallelograms.size() + L.dyn_traced.size());
     boxes.reserve(refs.capacity());
-    for (size_t i = 0; i < L.spheres.size(); i++) { refs.push_back(make_ref(PT_SPHERE, uint32_t(i))); boxes.push_back(sphere_box(L.spheres[i], reach)); }
+    refs.resize(L.spheres.size());
+    boxes.resize(L.spheres.size());
+    parallel_for(L.spheres.size(), [&](size_t i) { refs[i] = make_ref(PT_SPHERE, uint32_t(i)); boxes[i] = sphere_box(L.spheres[i], reach); });
     for (size_t i = 0; i < L.cubes.size(); i++) { refs.push_back(make_ref(PT_CUBE, uint32_t(i))); boxes.push_back(cube_box(L.cubes[i], reach)); }
     for (size_t i = 0; i < L.triangles.size(); i++) { refs.push_back(make_ref(PT_TRI, uint32_t(i))); boxes.push_back(bary_box(L.triangles[i], false, reach)); }
     for (size_t i = 0; i < L.parallelograms.size(); i++) { refs.push_back(make_ref(PT_PARA, uint32_t(i))); boxes.push_back(bary_box(L.parallelograms[i], true, reach)); }
@@ -481,15 +501,17 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     out.hot.reserve(28 * wide.nodes.size() + 12 * (L.spheres.size() + L.cubes.size()) + 16 * (L.triangles.size() + L.parallelograms.size()) + 4096);
     Packer hot(out.hot);
     h.off_nodes = hot.units();
-    for (const omb::Node4& nd : wide.nodes) {
-        hot.f4(nd.lox[0], nd.lox[1], nd.lox[2], nd.lox[3]); hot.f4(nd.hix[0], nd.hix[1], nd.hix[2], nd.hix[3]);
-        hot.f4(nd.loy[0], nd.loy[1], nd.loy[2], nd.loy[3]); hot.f4(nd.hiy[0], nd.hiy[1], nd.hiy[2], nd.hiy[3]);
-        hot.f4(nd.loz[0], nd.loz[1], nd.loz[2], nd.loz[3]); hot.f4(nd.hiz[0], nd.hiz[1], nd.hiz[2], nd.hiz[3]);
-        hot.u4(uint32_t(nd.child[0]), uint32_t(nd.child[1]), uint32_t(nd.child[2]), uint32_t(nd.child[3]));
+    {
+        static_assert(sizeof(omb::Node4) == 16 * U_NODE4, "a wide node is packed as it lies in memory: six plane quads, then the child references");
+        float* dst = hot.grow(size_t(U_NODE4) * wide.nodes.size());
+        parallel_for(wide.nodes.size(), [&](size_t i) { memcpy(dst + 4 * U_NODE4 * i, &wide.nodes[i], sizeof(omb::Node4)); });
     }
     h.off_node_far = hot.units();
     if (h.dyn_pad != 0.f) {
-        for (const omb::Node4& nd : wide.nodes) {
+        float* dst = hot.grow(wide.nodes.size());
+        parallel_for(wide.nodes.size(), [&](size_t i) {
+            const omb::Node4& nd = wide.nodes[i];
+            float* o4 = dst + 4 * i;
             double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
             for (int j = 0; j < 4; j++) {
                 if (!(nd.lox[j] <= nd.hix[j])) continue;  // empty slot
@@ -497,15 +519,19 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
                 lo[1] = std::min(lo[1], double(nd.loy[j])); hi[1] = std::max(hi[1], double(nd.hiy[j]));
                 lo[2] = std::min(lo[2], double(nd.loz[j])); hi[2] = std::max(hi[2], double(nd.hiz[j]));
             }
-            if (!(lo[0] <= hi[0])) { hot.f4(0.f, 0.f, 0.f, 0.f); continue; }
+            if (!(lo[0] <= hi[0])) { o4[0] = o4[1] = o4[2] = o4[3] = 0.f; return; }
             const float c[3] = {float(0.5 * (lo[0] + hi[0])), float(0.5 * (lo[1] + hi[1])), float(0.5 * (lo[2] + hi[2]))};
             double r2 = 0;  // from the ROUNDED centre to the farthest corner
             for (int a = 0; a < 3; a++) { const double d = std::max(std::fabs(lo[a] - double(c[a])), std::fabs(hi[a] - double(c[a]))); r2 += d * d; }
-            hot.f4(c[0], c[1], c[2], std::nextafter(float(std::sqrt(r2) * (1.0 + 1e-6)), std::numeric_limits<float>::infinity()));
-        }
+            o4[0] = c[0]; o4[1] = c[1]; o4[2] = c[2];
+            o4[3] = std::nextafter(float(std::sqrt(r2) * (1.0 + 1e-6)), std::numeric_limits<float>::infinity());
+        });
     }
     h.off_hot[PT_SPHERE] = hot.units();
-    for (const om_sphere& s : L.spheres) hot.rows3(s.m_world_to_local);
+    {
+        float* dst = hot.grow(3 * L.spheres.size());
+        parallel_for(L.spheres.size(), [&](size_t i) { memcpy(dst + 12 * i, L.spheres[i].m_world_to_local, 48); });  // rows 0-2
+    }
     h.off_hot[PT_CUBE] = hot.units();
     for (const om_cube& s : L.cubes) hot.rows3(s.m_world_to_local);
     auto pack_bary = [&](const om_barycentric& b) {
@@ -616,7 +642,10 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     out.cold.reserve(12 * (L.spheres.size() + L.cubes.size()) + 8 * out.n_total + 4096);
     Packer cold(out.cold);
     h.off_sph_l2w = cold.units();
-    for (const om_sphere& s : L.spheres) cold.rows3(s.m_local_to_world);
+    {
+        float* dst = cold.grow(3 * L.spheres.size());
+        parallel_for(L.spheres.size(), [&](size_t i) { memcpy(dst + 12 * i, L.spheres[i].m_local_to_world, 48); });
+    }
     h.off_cube_l2w = cold.units();
     for (const om_cube& s : L.cubes) cold.rows3(s.m_local_to_world);
     h.off_tdyn_l2w = cold.units();
@@ -625,7 +654,8 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     uint32_t base = 0;
     auto mats = [&](uint32_t pt, auto const& list) {
         h.mat_base[pt] = base;
-        for (size_t i = 0; i < list.size(); i++) pack_material(cold, list[i].material, pt, i);
+        float* dst = cold.grow(2 * list.size());
+        parallel_for(list.size(), [&](size_t i) { pack_material(dst + 8 * i, list[i].material, pt, i); });
         base += uint32_t(list.size());
     };
     mats(PT_SPHERE, L.spheres); mats(PT_CUBE, L.cubes); mats(PT_TRI, L.triangles); mats(PT_PLANE, L.infinite_planes);
@@ -644,6 +674,10 @@ std::string freeze(const omh::SceneLists& L, const om_camera* cam, uint32_t flag
     h.hot_units = hot.units();
     h.cold_units = cold.units();
     lap("marched structures");
+    if (timing) {  // the images' checksum: a refactoring of this file must not move it
+        auto fnv = [](const std::vector<float>& v) { uint64_t x = 1469598103934665603ull; const unsigned char* b = reinterpret_cast<const unsigned char*>(v.data()); for (size_t i = 0; i < v.size() * 4; i++) { x ^= b[i]; x *= 1099511628211ull; } return x; };
+        fprintf(stderr, "[om freeze] hot %zu floats fnv %016llx, cold %zu floats fnv %016llx\n", out.hot.size(), (unsigned long long)fnv(out.hot), out.cold.size(), (unsigned long long)fnv(out.cold));
+    }
     return std::string();
 }
 

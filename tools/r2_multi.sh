@@ -7,4 +7,4 @@ run --adaptive --spp 256 --steps 3 --warmup 1 > $O/bench_C2_adaptive_${N}gpu.jso
 python -m pytest tests -m gpu -x -q -k "dist or multi" > $O/pytest.log 2>&1; tail -2 $O/pytest.log
 cat $O/bench_C2_${N}gpu.json | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['e2e']['value'], d.get('phase_ms'), d.get('merge_check'))"
 cat $O/bench_C2_adaptive_${N}gpu.json | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['e2e']['value'], d.get('merge_check'))"
-tail -5 $O/*.err
+for f in $O/*.err; do tail -n 3 $f; done
