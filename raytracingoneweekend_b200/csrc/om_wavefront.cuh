@@ -31,7 +31,10 @@ using namespace omk::wf;
 #ifndef OM_WF_EXT_MIN_CTAS
 #define OM_WF_EXT_MIN_CTAS 2  // CTAs per SM the extend kernel is compiled for (64 registers at 2)
 #endif
-constexpr int WF_EXT_THREADS = 512;
+#ifndef OM_WF_EXT_THREADS
+#define OM_WF_EXT_THREADS 512
+#endif
+constexpr int WF_EXT_THREADS = OM_WF_EXT_THREADS;
 constexpr int WF_THREADS = 256;
 constexpr uint32_t WF_DESTS = (uint32_t)omk::wf::N_CLS + 1u;                 // shade classes + the march queue
 constexpr size_t WF_STAGE_BYTES = size_t(WF_EXT_THREADS / 32) * WF_DESTS * 32u * 4u;  // k_wf_extend: per-warp staging of retired slots
