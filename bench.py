@@ -274,7 +274,7 @@ def run_ours(args):
 
     def make_job(frozen):
         if args.adaptive:
-            s = D.AdaptiveScheduler(frozen, cam, W, H, spp, rank, world, pass_spp=args.pass_spp, device=local, rebalance=False, **kw)
+            s = D.AdaptiveScheduler(frozen, cam, W, H, spp, rank, world, pass_spp=args.pass_spp, device=local, rebalance=False, refresh_every=args.refresh_every, **kw)
             s.r.set_stream(stream.cuda_stream)
             return s
         d = D.DistributedRenderer(frozen, cam, W, H, spp, rank, world, mode="spp", device=local, **kw)
@@ -452,7 +452,7 @@ def run_ours(args):
                     osc.add(k, arr)
             rate, threads, desc, _ = cpu_reference_rate(WORKLOADS[args.workload], seconds_target=12.0, osc=osc)
             cpu = {"value": rate, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": desc}
-        mode = "adaptive (bad_avgs >= 5 retires a pixel), max %d spp, passes of %d" % (spp, args.pass_spp) if args.adaptive else "fixed spp"
+        mode = ("adaptive (bad_avgs >= 5 retires a pixel), max %d spp, passes of %d, pixel states merged %s" % (spp, args.pass_spp, "after the last pass" if args.refresh_every == 0 else "every %d pass(es)" % args.refresh_every)) if args.adaptive else "fixed spp"
         line = {
             "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
@@ -493,6 +493,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--wavefront", action="store_true", help="use the global wavefront pipeline (OM_RENDER_WAVEFRONT) instead of the library's choice")
     ap.add_argument("--pool", action="store_true", help="use the CTA-resident wavefront (OM_RENDER_POOL)")
+    ap.add_argument("--refresh-every", type=int, default=0, help="--adaptive on N GPUs: merge the pixel states on every rank after every k-th pass (1 = the viewer's refresh); 0 = once, after the last pass")
     ap.add_argument("--adaptive", action="store_true", help="the reference's adaptive mode (OM_RENDER_ADAPTIVE) through dist.AdaptiveScheduler; value counts the samples actually traced")
     ap.add_argument("--pass-spp", type=int, default=16, help="--adaptive: samples per pass between retirement checks / exchanges")
     args = ap.parse_args()

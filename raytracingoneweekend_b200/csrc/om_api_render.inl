@@ -703,6 +703,9 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
 }
 
 namespace {
+#ifndef OM_SPREAD_MAX_LIVE_DEFAULT
+#define OM_SPREAD_MAX_LIVE_DEFAULT 250000u  // live pixels at or below which an adaptive pass runs on k_render_spread (measured, profiles/r2_experiments.md section 9)
+#endif
 om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
     omk::RenderArgs a = make_args(r);
     if (pilot) a.tile_cost = r->tile_cost;
@@ -730,8 +733,25 @@ om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
     } else {
         cudaError_t e;
         if (r->use_pool) e = exact ? om_exact::launch_render_pool(a, count, r->pool_grid, r->pool_smem_bytes, r->stream) : om_fast::launch_render_pool(a, count, r->pool_grid, r->pool_smem_bytes, r->stream);
-        else e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
-                       : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+        else {
+            // Adaptive passes over a live list: when few pixels are left a pass is as long as its hardest pixel's chain of samples; then
+            // k_render_spread lets several lanes share a pixel.  Which of the two kernels renders the pass is decided ON THE DEVICE from
+            // the live count (no host synchronisation): both are launched, the other one returns at once.
+            const bool spread = adaptive && a.live_list != nullptr && !count && !pilot && !getenv("OM_NO_SPREAD");
+            if (spread) {
+                uint32_t sp = 1u;
+                while (sp * 2u <= 32u && sp * 2u <= a.spp_pass) sp *= 2u;
+                const char* mx = getenv("OM_SPREAD_MAX_LIVE");
+                a.spread = sp;
+                a.spread_max = sp >= 2u ? (mx ? (uint32_t)strtoul(mx, nullptr, 10) : OM_SPREAD_MAX_LIVE_DEFAULT) : 0u;
+            }
+            e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
+                      : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+            if (e == cudaSuccess && a.spread_max != 0u) {
+                e = exact ? om_exact::launch_render_spread(a, r->use_smem, r->grid, r->smem_bytes, r->stream) : om_fast::launch_render_spread(a, r->use_smem, r->grid, r->smem_bytes, r->stream);
+                r->kernels++;
+            }
+        }
         if (e != cudaSuccess) { r->pool.push_back(ev); return fail(OM_ERR_CUDA, "k_render launch failed: %s", cudaGetErrorString(e)); }
         r->kernels++;
     }

@@ -45,6 +45,10 @@ struct RenderArgs {
     // (most expensive first) or nullptr = row order; and where k_render leaves each tile's cost (cycles / 16) for the next order
     const uint32_t* block_order;
     uint32_t* tile_cost;
+    // Adaptive passes over a compacted live list (k_render_spread, om_device.cuh): when at most spread_max pixels are live, `spread`
+    // lanes share a pixel, each traces one of its next samples, and the results are folded into the pixel's Stats in sample order.
+    // 0 = never.  Both kernels are launched; each looks at *live_count and the one whose turn it is not returns at once.
+    uint32_t spread_max, spread;
 };
 
 // Wavefront pipeline (om_wavefront.cuh).  A SLOT carries one path; it is bound to one pixel until

@@ -1219,6 +1219,7 @@ __device__ __forceinline__ void stage_scene_smem(const float4* hot_g, uint32_t u
 // ============================================================================================
 template <bool SMEM, bool COUNT, int MA>
 __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(const __grid_constant__ RenderArgs A) {
+    if (A.spread_max != 0u && A.live_count != nullptr && *A.live_count <= A.spread_max) return;  // k_render_spread's pass
     if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
     SceneView<SMEM> sv;
     sv.hot_g = A.hot_g;
@@ -1411,6 +1412,127 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         unsigned long long li = lane_iters;
         for (int o = 16; o > 0; o >>= 1) li += __shfl_xor_sync(0xffffffffu, li, o);
         if ((threadIdx.x & 31) == 0) { atomicAdd(&A.counters[CTR_WARP_ITERS], (unsigned long long)warp_iters); atomicAdd(&A.counters[CTR_LANE_ITERS], li); }
+    }
+}
+
+// ============================================================================================
+// k_render_spread: adaptive passes with few live pixels.  In k_render a lane owns a pixel and traces its samples one after
+// the other, so a pass is as long as its hardest pixel's chain of spp_pass paths (depth-50 glass paths: 8 ms for a pass of
+// 16 however few pixels are live, and the same on every GPU of a multi-GPU render).  Here `spread` (a power of two <= 32)
+// consecutive lanes share one pixel of the live list: in each round lane i of the group traces sample n + i, then every
+// lane of the group folds the round's results into its own copy of the pixel's Stats in sample order - the same adds in the
+// same order as the sequential loop, so the Stats are bit-identical - and stops at the sample that retires the pixel
+// (render_thread.rs:194-200); the samples traced past that point are thrown away and not counted.
+// Plain structure (no phase alignment, no tile costs, marches run to their end): these passes are latency-, not issue-bound.
+// ============================================================================================
+template <bool SMEM, int MA>
+__global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render_spread(const __grid_constant__ RenderArgs A) {
+    if (A.live_count == nullptr || *A.live_count > A.spread_max) return;  // k_render's pass
+    if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
+    SceneView<SMEM> sv;
+    sv.hot_g = A.hot_g;
+    sv.cold_g = A.cold_g;
+    const SceneHeader& S = A.scene;
+    const bool brute = (A.flags & OM_RENDER_BRUTE_FORCE) != 0;
+    const bool adaptive = (A.flags & OM_RENDER_ADAPTIVE) != 0;
+    Counters cn = {0, 0, 0, 0, 0, 0, 0};
+    unsigned long long credited = 0, traced = 0;
+    const uint32_t lane = threadIdx.x & 31u;
+    TravStack<SMEM, RENDER_THREADS> stack;
+    stack.init(S.hot_units);
+    const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;
+    const uint32_t SP = A.spread, sub = lane & (SP - 1u), lead = lane & ~(SP - 1u);
+    const uint32_t n_live = *A.live_count;
+    const unsigned long long n_slots = (unsigned long long)n_live * SP;
+    for (;;) {
+        uint32_t ticket = 0;
+        if (lane == 0u) ticket = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], 1ull);
+        ticket = __shfl_sync(FULL, ticket, 0);
+        if ((unsigned long long)ticket * 32ull >= n_slots) break;
+        const uint32_t pi = (ticket * 32u + lane) / SP;
+        const uint32_t pxl = pi < n_live ? A.live_list[pi] : 0xFFFFFFFFu;
+        // every lane of a group keeps its own copy of the pixel's Stats (the folds below are the same on all of them)
+        Stats st;
+        st.sum = v3(0.f, 0.f, 0.f); st.n = 0; st.avg_depth = 0.f; st.bad_avgs = 0; st.bloom_lo = 0; st.bloom_hi = 0; st.color = 0;
+        uint32_t todo = 0;
+        if (pxl != 0xFFFFFFFFu) {
+            const float4 a = A.acc[pxl];
+            const uint4 x = A.aux[pxl];
+            st.sum = v3(a.x, a.y, a.z); st.n = __float_as_uint(a.w);
+            st.avg_depth = __uint_as_float(x.x); st.bad_avgs = x.y; st.bloom_lo = x.z; st.bloom_hi = x.w;
+            st.color = stats_color_of(st.sum, st.n);
+            todo = A.spp_budget > st.n ? min(A.spp_budget - st.n, A.spp_pass) : 0u;
+            if (A.n_target) { const uint32_t tg = min(A.spp_budget, A.n_target); todo = tg > st.n ? tg - st.n : 0u; }
+            if (adaptive && st.bad_avgs >= 5u) todo = 0u;
+        }
+        const bool touched = todo > 0u;
+        while (__any_sync(FULL, todo > 0u)) {
+            // ---- one round: lane `sub` of a group traces sample st.n + sub ----
+            bool tracing = sub < todo;
+            Rng g;
+            rng_init(g, A.rk, 0u, 0u);
+            g.b0 = g.b1 = g.b2 = g.b3 = 0u;
+            Ray ray;
+            ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
+            V3 color = v3(1.f, 1.f, 1.f), result = v3(0.f, 0.f, 0.f);
+            uint32_t seg = 0, first_lo = 0, first_hi = 0;
+            float first_t = kInf;
+            if (tracing) {
+                const uint32_t sample = A.sample_base + st.n + sub;  // jitters[pixel.stats.n]
+                rng_init(g, A.rk, pxl, sample);
+                ray = primary_ray(A, pxl, sample, g);
+            }
+            while (__any_sync(FULL, tracing)) {
+                Hit h = closest_hit_warp<SMEM, false, MA>(sv, S, ray, A.tmin, A.tmax, brute, tracing, cn, stack);
+                if (tracing) {
+                    if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
+                        finish_hit<SMEM, MA == 3>(sv, S, ray, A.tmin, h);
+                        const Material m = load_material(sv, S, h.ref);
+                        if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
+                        color = color * scatter(m, ray, h.point, h.normal, g);
+                        seg++;
+                        if (seg >= nseg) { result = -v3(0.f, 0.f, 0.f); tracing = false; }  // out of depth: -black (:142)
+                    } else {  // None: sky (:117-123)
+                        const float t = 0.5f * (ray.d.y + 1.0f);
+                        const V3 sky = (1.0f - t) * v3(1.f, 1.f, 1.f) + t * v3(0.5f, 0.7f, 1.0f);
+                        result = color * sky;
+                        tracing = false;
+                    }
+                }
+            }
+            // ---- fold the round into the Stats, sample by sample ----
+            const uint32_t round_n = min(todo, SP);
+            bool retired = false;
+            for (uint32_t i = 0; i < SP; i++) {  // (warp-uniform trip count; groups with a shorter round skip)
+                const uint32_t src = lead + i;
+                const float rx = __shfl_sync(FULL, result.x, src), ry = __shfl_sync(FULL, result.y, src), rz = __shfl_sync(FULL, result.z, src);
+                const float ft = __shfl_sync(FULL, first_t, src);
+                const uint32_t flo = __shfl_sync(FULL, first_lo, src), fhi = __shfl_sync(FULL, first_hi, src);
+                if (i < round_n && !retired) {
+                    bool done = stats_add(st, v3(rx, ry, rz), ft, flo, fhi);
+                    if (!adaptive) done = false;
+                    if (sub == 0u) {
+                        traced++;
+                        const uint32_t left = A.spp_budget - st.n;
+                        credited += (done ? (unsigned long long)left : 0ull) + 1ull;  // render_thread.rs:196-198
+                    }
+                    if (done) retired = true;
+                }
+            }
+            todo = retired ? 0u : todo - round_n;
+        }
+        if (touched && sub == 0u) {
+            A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
+            A.aux[pxl] = make_uint4(__float_as_uint(st.avg_depth), st.bad_avgs, st.bloom_lo, st.bloom_hi);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        credited += __shfl_xor_sync(FULL, credited, o);
+        traced += __shfl_xor_sync(FULL, traced, o);
+    }
+    if (lane == 0u) {
+        if (credited) atomicAdd(&A.counters[CTR_CREDITED], credited);
+        if (traced) atomicAdd(&A.counters[CTR_TRACED], traced);
     }
 }
 

@@ -47,6 +47,18 @@ cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int g
     return cudaGetLastError();
 }
 
+// k_render_spread<SMEM, MA> (adaptive passes with few live pixels; same block size and shared-memory layout as k_render)
+cudaError_t launch_render_spread(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st) {
+    const int ma = scene_march_variant(a);
+    auto go = [&](auto kern) {
+        if (smem) prep(kern, smem_bytes);
+        kern<<<grid, RENDER_THREADS, smem ? smem_bytes : 0, st>>>(a);
+    };
+    if (smem) { if (ma == 1) go(k_render_spread<true, 1>); else if (ma == 3) go(k_render_spread<true, 3>); else go(k_render_spread<true, 0>); }
+    else { if (ma == 1) go(k_render_spread<false, 1>); else if (ma == 3) go(k_render_spread<false, 3>); else go(k_render_spread<false, 0>); }
+    return cudaGetLastError();
+}
+
 cudaError_t launch_primary(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st, uint32_t mode, uint32_t sample_index,
                            unsigned long long* ids, float* t) {
     if (smem) { prep(k_primary<true>, smem_bytes); k_primary<true><<<grid, CTA_THREADS, smem_bytes, st>>>(a, mode, sample_index, ids, t); }

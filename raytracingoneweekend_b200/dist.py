@@ -179,18 +179,24 @@ class AdaptiveScheduler:
     pixel has exactly one owner, the others contribute zeros, so the sum is the owner's bits) and loaded into every handle.
     The image is bit-identical to a single-GPU adaptive render; rank 0 can read it after any pass (`on_pass`)."""
 
-    def __init__(self, frozen, cam, width, height, spp, rank, world, pass_spp=8, device=None, rebalance=False, **kw):
+    def __init__(self, frozen, cam, width, height, spp, rank, world, pass_spp=8, device=None, rebalance=False, refresh_every=1, **kw):
+        """refresh_every: the pixel states are merged on every rank after every k-th pass (1 = the viewer's refresh after each pass,
+        the reference's main loop reads the shared pixels whenever it redraws); 0 = only once, after the last pass.  Between merges a
+        rank keeps rendering its own chunks from its own state and the ranks exchange two integers per pass (samples credited,
+        live pixels).  Re-dealing (`rebalance`) moves pixels between ranks and therefore merges after every pass."""
         import torch
         from . import api
 
         self.torch = torch
         self.rank, self.world, self.pass_spp, self.rebalance, self.spp = rank, world, max(1, pass_spp), rebalance, spp
+        self.refresh_every = 1 if rebalance else max(0, int(refresh_every))
         self.device = torch.cuda.current_device() if device is None else device
         flags = kw.pop("flags", 0) | A.RENDER_ADAPTIVE
         self.r = api.Renderer(frozen, cam, api.render_params(width, height, spp, flags=flags, device=self.device, **kw))
         self.state = torch.empty((width * height, 8), dtype=torch.int32, device=torch.device("cuda", self.device))
         self.owners = (np.arange(self.r.n_chunks) % max(world, 1)).astype(np.uint8)
         self.credited = 0
+        self.merges = 0
         self.history = []  # per pass: (live pixels before the pass, live pixels per rank)
 
     def _all_reduce(self, t):
@@ -198,33 +204,53 @@ class AdaptiveScheduler:
             import torch.distributed as dist
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
 
+    def merge(self):
+        """Every rank's handle gets the whole frame: the raw states of the owned chunks, summed over the ranks (one owner per pixel)."""
+        self.r.export_state(self.state.data_ptr(), only_owned=True)
+        self._all_reduce(self.state)
+        if self.world > 1:
+            self.torch.cuda.synchronize(self.device)
+        self.r.import_state(self.state.data_ptr())
+        self.merges += 1
+
     def run(self, on_pass=None):
         torch = self.torch
         total = self.r.npx * self.spp
+        own = None
         live = self.r.live_per_chunk()
-        done_spp, seen = 0, 0
-        while done_spp < self.spp and int(live.sum()) > 0:
+        load = np.array([int(live[self.owners == k].sum()) for k in range(self.world)])  # (every rank starts from the same state)
+        done_spp, seen, passes, merged_at = 0, 0, 0, 0
+        self.r.set_chunk_owners(self.owners, self.rank)
+        while done_spp < self.spp and int(load.sum()) > 0:
             if self.rebalance:
                 self.owners, load = deal_chunks(live, self.world)
-            else:
-                load = np.array([int(live[self.owners == k].sum()) for k in range(self.world)])
-            self.history.append((int(live.sum()), load.tolist()))
-            self.r.set_chunk_owners(self.owners, self.rank)
+                self.r.set_chunk_owners(self.owners, self.rank)
+                own = None
+            if own is None:
+                own = self.owners == self.rank
+            self.history.append((int(load.sum()), load.tolist()))
             self.r.launch(self.pass_spp)
-            self.r.export_state(self.state.data_ptr(), only_owned=True)
-            self._all_reduce(self.state)
-            if self.world > 1:
-                torch.cuda.synchronize(self.device)
-            self.r.import_state(self.state.data_ptr())
-            mine = self.r.samples_done()
-            delta = torch.tensor([mine - seen], dtype=torch.int64, device=self.state.device)
-            seen = mine
-            self._all_reduce(delta)
-            self.credited += int(delta.item())  # the AtomicU64 of main.rs:148, summed over the ranks
+            passes += 1
             done_spp += self.pass_spp
+            merge_now = self.refresh_every > 0 and passes % self.refresh_every == 0
+            if merge_now:
+                self.merge()
+                merged_at = passes
+            mine = self.r.samples_done()
             live = self.r.live_per_chunk()
+            # two integers per rank and pass: the samples credited (the AtomicU64 of main.rs:148) and the live pixels of its own chunks
+            box = torch.zeros((self.world, 2), dtype=torch.int64, device=self.state.device)
+            box[self.rank, 0] = mine - seen
+            box[self.rank, 1] = int(live[own].sum())
+            seen = mine
+            self._all_reduce(box)
+            got = box.cpu().numpy()
+            self.credited += int(got[:, 0].sum())
+            load = got[:, 1].astype(np.int64)
             if on_pass is not None:
                 on_pass(self)
+        if merged_at != passes and self.world > 1:
+            self.merge()  # the frame after the last pass
         assert self.credited <= total
         return self.credited
 
