@@ -265,6 +265,36 @@ def test_render_bit_exact_adaptive_multipass(api, A, rtiow):
     r.close()
 
 
+@pytest.mark.parametrize("kind,seed,pass_spp", [("glass_heavy", 4, 16), ("random_scene", 1, 3), ("random_scene", 1, 40), ("marched", 3, 8)])
+def test_adaptive_spread_passes_bit_exact(api, A, O, kind, seed, pass_spp, monkeypatch):
+    """Adaptive passes after the first walk a compacted live list; with few live pixels they run on k_render_spread (2..32 lanes
+    per pixel, one sample each, folded in sample order).  Pixels, credited and traced samples must equal the oracle's sequential
+    adaptive render - also when a pass is not a whole number of rounds (pass_spp 3 and 40) - and the k_render-only path's."""
+    fz = api.FrozenHittableList.generate(kind, seed)
+    osc = oracle_scene_from(O, fz)
+    cam = cam_rtiow(api, 4 / 3)
+    W, H, spp = 72, 54, 50
+    p = api.render_params(W, H, spp, seed=31, flags=A.RENDER_ADAPTIVE)
+    ref = osc.render(cam, p)
+
+    def render():
+        r = api.Renderer(fz, cam, p)
+        for _ in range((spp + pass_spp - 1) // pass_spp):
+            r.launch(pass_spp)
+        r.sync()
+        out = (r.read_pixels().copy(), r.samples_done(), r.samples_traced(), r.perf_counters()["kernels"])
+        r.close()
+        return out
+
+    g, credited, traced, kernels = render()
+    assert_pixels_equal(g, ref["pixels"])
+    assert credited == ref["credited"] == W * H * spp and traced == ref["traced"] < W * H * spp
+    monkeypatch.setenv("OM_NO_SPREAD", "1")
+    g2, credited2, traced2, kernels2 = render()
+    assert g2.tobytes() == g.tobytes() and (credited2, traced2) == (credited, traced)
+    assert kernels > kernels2  # the spread kernel really was launched beside k_render
+
+
 def test_render_bit_exact_marched_and_mixed(api, A, mixed, O):
     fz, osc = mixed
     cam = api.Camera.new((6, 3, 7), (0, 0.5, 0), (0, 1, 0), 40.0, 1.5, 0.05, 9.0)
