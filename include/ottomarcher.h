@@ -427,6 +427,11 @@ OM_API om_status om_render_import_accum(om_render* r, const float* dev_acc, cons
  * integer SUM over the ranks (NCCL all-reduce) reassembles the frame, om_render_import_state loads it
  * into every handle, and om_render_live_per_chunk says how many pixels of each chunk still want samples
  * (the input of the next deal).  Results are those of one handle rendering alone, bit for bit.
+ * With a table that does not change, a handle needs only its own chunks' state between passes: the exchange
+ * can then wait until the frame is wanted (after the last pass, or whenever a viewer refreshes).
+ * Adaptive passes over few live pixels (at most 250 000 on the handle) are rendered by a second kernel in
+ * which 2..32 lanes share a pixel and fold their samples into its Stats in sample order - the same bits,
+ * without a pass lasting as long as the hardest pixel's chain of samples.
  * owners == NULL returns the handle to the static rule of om_render_params.                          */
 OM_API om_status om_render_set_chunk_owners(om_render* r, const uint8_t* owners, size_t n_chunks, uint32_t my_id);
 OM_API om_status om_render_export_state(om_render* r, uint32_t* dev_state, uint32_t only_owned);
