@@ -78,12 +78,18 @@ __device__ __forceinline__ bool pixel_is_mine(uint32_t i, uint32_t part_rank, ui
     if (owners) return owners[i / OM_CHUNK_PIXELS] == my_id;
     return part_world <= 1u || ((i / OM_CHUNK_PIXELS) % part_world) == part_rank;
 }
-__global__ void k_compact_live(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t npx, uint32_t budget, uint32_t adaptive,
+// The list is written in the render kernel's tile order (a warp here = an 8x4 tile, a CTA = a 16x16 block), so that the 32 live pixels
+// a render warp takes from it are neighbours in both directions: strips of 32 pixels of one image row mixed more kinds of pixels per
+// warp (lane occupancy of the adaptive passes 0.59 against 0.72 for tiles; the warp waits for its longest pixel).
+__global__ void k_compact_live(const float4* __restrict__ acc, const uint4* __restrict__ aux, uint32_t width, uint32_t height, uint32_t budget, uint32_t adaptive,
                                uint32_t part_rank, uint32_t part_world, const uint8_t* __restrict__ owners, uint32_t my_id, uint32_t* __restrict__ list,
                                uint32_t* __restrict__ count) {
-    const uint32_t i = blockIdx.x * UT + threadIdx.x;
+    const uint32_t t = blockIdx.x * UT + threadIdx.x, tile = t >> 5, in = t & 31u;
+    const uint32_t tiles_x = (width + 7u) / 8u, bx_n = (tiles_x + 1u) >> 1, blk = tile >> 3, k = tile & 7u;
+    const uint32_t x = ((blk % bx_n) * 2u + (k & 1u)) * 8u + (in & 7u), y = ((blk / bx_n) * 4u + (k >> 1)) * 4u + (in >> 3);
+    const uint32_t i = y * width + x;
     bool live = false;
-    if (i < npx) {
+    if (x < width && y < height) {
         const bool mine = pixel_is_mine(i, part_rank, part_world, owners, my_id);
         const uint32_t n = __float_as_uint(acc[i].w);
         live = mine && n < budget && !(adaptive && aux[i].y >= 5u);
@@ -703,6 +709,8 @@ om_status om_render_launch(om_render* r, uint32_t spp_this_pass) {
 }
 
 namespace {
+// one CTA of k_compact_live per 16x16 block of pixels
+int compact_blocks(const om_render* r) { const uint32_t tx = (r->p.width + 7u) / 8u, ty = (r->p.height + 3u) / 4u; return int(((tx + 1u) / 2u) * ((ty + 3u) / 4u)); }
 #ifndef OM_SPREAD_MAX_LIVE_DEFAULT
 #define OM_SPREAD_MAX_LIVE_DEFAULT 250000u  // live pixels at or below which an adaptive pass runs on k_render_spread (measured, profiles/r2_experiments.md section 9)
 #endif
@@ -714,7 +722,7 @@ om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
     if (r->owners) {  // scheduled ownership: the pixels to walk are decided now, from the state and the table of this moment
         if (!r->live_list) { CU(dev_alloc(&r->live_list, size_t(r->npx) * sizeof(uint32_t))); CU(cudaMalloc(&r->live_count, sizeof(uint32_t))); }
         CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
-        k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, adaptive ? 1u : 0u, 0u, 1u, r->owners, r->owner_id, r->live_list, r->live_count);
+        k_compact_live<<<compact_blocks(r), UT, 0, r->stream>>>(r->acc, r->aux, r->p.width, r->p.height, r->budget, adaptive ? 1u : 0u, 0u, 1u, r->owners, r->owner_id, r->live_list, r->live_count);
         CU(cudaGetLastError());
         r->kernels++;
         r->have_live = true;
@@ -758,7 +766,7 @@ om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
     r->n_uniform = n_target;
     if (adaptive && !r->owners) {  // next pass walks only the pixels that still want samples
         CU(cudaMemsetAsync(r->live_count, 0, sizeof(uint32_t), r->stream));
-        k_compact_live<<<ublocks(r->npx), UT, 0, r->stream>>>(r->acc, r->aux, r->npx, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, nullptr, 0u, r->live_list, r->live_count);
+        k_compact_live<<<compact_blocks(r), UT, 0, r->stream>>>(r->acc, r->aux, r->p.width, r->p.height, r->budget, 1u, r->p.part_rank, r->p.part_world ? r->p.part_world : 1u, nullptr, 0u, r->live_list, r->live_count);
         CU(cudaGetLastError());
         r->kernels++;
         r->have_live = true;

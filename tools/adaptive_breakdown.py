@@ -4,13 +4,13 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."
 import numpy as np, torch
 import bench
 from raytracingoneweekend_b200 import api, dist, _abi as A
-ap = argparse.ArgumentParser(); ap.add_argument("--spp", type=int, default=256); ap.add_argument("--pass-spp", type=int, default=16); ap.add_argument("--workload", default="C2")
+ap = argparse.ArgumentParser(); ap.add_argument("--spp", type=int, default=256); ap.add_argument("--pass-spp", type=int, default=16); ap.add_argument("--workload", default="C2"); ap.add_argument("--flags", type=int, default=0)
 a = ap.parse_args()
 kind, seed, n_param, W, H, spp, aspect = bench.WORKLOADS[a.workload]
 fz = api.FrozenHittableList.generate(kind, seed, n_param)
 cam = bench.make_camera(api, aspect)
 for rep in range(2):
-    s = dist.AdaptiveScheduler(fz, cam, W, H, a.spp, 0, 1, pass_spp=a.pass_spp)
+    s = dist.AdaptiveScheduler(fz, cam, W, H, a.spp, 0, 1, pass_spp=a.pass_spp, flags=a.flags)
     r = s.r
     T = {}
     def timed(name, fn):
@@ -28,7 +28,12 @@ for rep in range(2):
         timed("samples_done", r.samples_done)
         n_live = int(live.sum())
         live = timed("live_per_chunk", r.live_per_chunk)
-        per_pass.append((n_live, round((T["launch"] - t0) * 1e3, 2)))
+        row = (n_live, round((T["launch"] - t0) * 1e3, 2))
+        if a.flags & A.RENDER_COUNTERS:
+            c = r.perf_counters()
+            row += (round((c["lane_iters"] - getattr(s, "_li", 0)) / max(1, 32 * (c["warp_iters"] - getattr(s, "_wi", 0))), 3), c["traced"] - getattr(s, "_tr", 0), c["segments"] - getattr(s, "_sg", 0))
+            s._li, s._wi, s._tr, s._sg = c["lane_iters"], c["warp_iters"], c["traced"], c["segments"]
+        per_pass.append(row)
         done += a.pass_spp; passes += 1
     total = time.perf_counter() - t_all
     traced = r.samples_traced()
