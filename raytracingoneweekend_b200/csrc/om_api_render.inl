@@ -753,8 +753,12 @@ om_status launch_pass(om_render* r, uint32_t spp_this_pass, bool pilot) {
                 a.spread = sp;
                 a.spread_max = sp >= 2u ? (mx ? (uint32_t)strtoul(mx, nullptr, 10) : OM_SPREAD_MAX_LIVE_DEFAULT) : 0u;
             }
-            e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
-                      : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
+            // adaptive passes: a slot per lane (k_render_lanes) - a warp that owns a tile idles behind the pixel that retires last
+            // (passes of up to 64 samples: +6 % at 16, +3 % at 32, +1 % at 64; one 256-sample launch is bound by its hardest pixel's chain either way)
+            const bool lanes = adaptive && !count && !pilot && a.spp_pass <= 64u && !getenv("OM_NO_LANES");
+            if (lanes) e = exact ? om_exact::launch_render_lanes(a, r->use_smem, r->grid, r->smem_bytes, r->stream) : om_fast::launch_render_lanes(a, r->use_smem, r->grid, r->smem_bytes, r->stream);
+            else e = exact ? om_exact::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream)
+                           : om_fast::launch_render(a, r->use_smem, count, r->grid, r->smem_bytes, r->stream);
             if (e == cudaSuccess && a.spread_max != 0u) {
                 e = exact ? om_exact::launch_render_spread(a, r->use_smem, r->grid, r->smem_bytes, r->stream) : om_fast::launch_render_spread(a, r->use_smem, r->grid, r->smem_bytes, r->stream);
                 r->kernels++;

@@ -1211,6 +1211,121 @@ __device__ __forceinline__ void stage_scene_smem(const float4* hot_g, uint32_t u
     }
 }
 
+// Per-lane state of the path state machine (one path segment per loop iteration).
+struct PathLane {
+    Rng g;
+    Ray ray;
+    V3 color;
+    uint32_t seg;
+    float first_t;
+    uint32_t first_lo, first_hi;
+    bool fresh;
+    bool marching;       // BOUNDED: the lane's ray is part-way through its march
+    float m_t, pend_t;   // ... how far, and the traced hit that stands if the march finds nothing
+    uint32_t m_left, pend_ref;
+    __device__ __forceinline__ void init(const uint32_t* rk) {
+        rng_init(g, rk, 0u, 0u);
+        g.b0 = g.b1 = g.b2 = g.b3 = 0u;
+        ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
+        color = v3(1.f, 1.f, 1.f);
+        seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
+        fresh = true; marching = false; m_t = 0.f; pend_t = 0.f; m_left = 0xFFFFFFFFu; pend_ref = omd::REF_NONE;
+    }
+};
+struct PathTotals {
+    unsigned long long credited, traced;
+    uint32_t warp_iters, lane_iters;  // COUNT: lane occupancy of the path loop
+};
+
+// One iteration of the path loop for a whole warp: every lane with todo > 0 resolves (at most) one segment of its pixel's current
+// sample - new sample, closest hit, shade or sky, Stats::add at the end of a path.  Shared by k_render (a warp per tile) and
+// k_render_lanes (a slot per lane).
+template <bool SMEM, bool COUNT, int MA, class STK>
+__device__ __forceinline__ void path_iteration(const RenderArgs& A, const SceneView<SMEM>& sv, const SceneHeader& S, bool brute, bool adaptive, bool align, uint32_t nseg,
+                                               uint32_t pxl, Stats& st, uint32_t& todo, PathLane& L, Counters& cn, PathTotals& T, STK& stack) {
+    constexpr bool BOUNDED = OM_BOUNDED_MARCH_ALL || MA == 1 || MA == 3;  // scenes built around marched objects (C3); C2's kernel keeps march()
+    Rng& g = L.g;
+    Ray& ray = L.ray;
+    V3& color = L.color;
+    uint32_t& seg = L.seg;
+    float& first_t = L.first_t;
+    uint32_t &first_lo = L.first_lo, &first_hi = L.first_hi;
+    bool &fresh = L.fresh, &marching = L.marching;
+    float &m_t = L.m_t, &pend_t = L.pend_t;
+    uint32_t &m_left = L.m_left, &pend_ref = L.pend_ref;
+    unsigned long long &credited = T.credited, &traced = T.traced;
+    uint32_t &warp_iters = T.warp_iters, &lane_iters = T.lane_iters;
+    const bool alive = todo > 0u;
+    if (COUNT) { warp_iters++; lane_iters += alive ? 1u : 0u; }
+    if (align) phase_bar_count(1);
+    if (alive && fresh) {
+        const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
+        rng_init(g, A.rk, pxl, sample);
+        ray = primary_ray(A, pxl, sample, g);
+        color = v3(1.f, 1.f, 1.f);
+        seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
+        fresh = false;
+    }
+    Hit h;
+    bool resolved = alive;  // this lane's segment is resolved in this iteration (shade it)
+    if constexpr (BOUNDED) {
+        // Bounded marching: a lane whose ray enters the marched objects' bounds sphere-traces at most OM_MARCH_STEPS steps per
+        // iteration and carries on in the next one, while the other lanes of the warp shade, start samples and traverse.
+        // (One call of march() ran as long as the warp's longest march: 5.6 of 32 lanes per instruction on C3.)
+        const bool trav = alive && !marching;
+        if (COUNT && trav) cn.segments++;
+        const Best b = closest_traced_warp<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, trav, cn, stack);
+        h.t = pend_t; h.ref = pend_ref; h.point = v3(0.f, 0.f, 0.f); h.normal = v3(0.f, 0.f, 0.f);
+        if (trav) {
+            h.t = b.t; h.ref = b.ref;
+            if (S.n_marched != 0u) {  // (see closest_hit_warp)
+                const RayInv q = ray_inv(ray);
+                if (slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, A.tmin, fminf(A.tmax, b.t)) < kInf) {
+                    marching = true; m_left = 0xFFFFFFFFu; m_t = 0.f; pend_t = b.t; pend_ref = b.ref;
+                }
+            }
+        }
+        if (alive && marching) {
+            Hit m;
+            const bool over = march_some<SMEM, COUNT, MA == 1, MA == 3>(sv, S, ray, A.tmin, A.tmax, pend_t, m_t, m_left, OM_MARCH_STEPS, m, &cn);
+            resolved = over;
+            if (over) { marching = false; if (m.ref != omd::REF_NONE) h = m; else { h.t = pend_t; h.ref = pend_ref; } }
+        }
+    } else {
+        h = closest_hit_warp<SMEM, COUNT, MA>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
+    }
+    if (align) phase_bar();
+    if (resolved) {
+        bool finished;
+        V3 result = color;
+        if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
+            finish_hit<SMEM, MA == 3>(sv, S, ray, A.tmin, h);
+            const Material m = load_material(sv, S, h.ref);
+            if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
+            color = color * scatter(m, ray, h.point, h.normal, g);
+            seg++;
+            finished = seg >= nseg;
+            if (finished) result = -v3(0.f, 0.f, 0.f);  // out of depth: -black (:142)
+        } else {  // None: sky (:117-123)
+            const float t = 0.5f * (ray.d.y + 1.0f);
+            const V3 sky = (1.0f - t) * v3(1.f, 1.f, 1.f) + t * v3(0.5f, 0.7f, 1.0f);
+            result = color * sky;
+            finished = true;
+        }
+        if (finished) {
+            bool done = stats_add(st, result, first_t, first_lo, first_hi);
+            if (!adaptive) done = false;
+            traced++;
+            todo--;
+            const uint32_t left = A.spp_budget - st.n;
+            credited += (done ? (unsigned long long)left : 0ull) + 1ull;  // render_thread.rs:196-198
+            if (done) todo = 0u;
+            fresh = true;
+        }
+    }
+
+}
+
 // ============================================================================================
 // k_render: persistent path-regeneration kernel.  One lane owns one pixel for the whole pass and
 // runs a per-lane state machine (new sample -> segment -> shade -> ... -> Stats::add), so lanes
@@ -1228,10 +1343,8 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
     const bool brute = (A.flags & OM_RENDER_BRUTE_FORCE) != 0;
     const bool adaptive = (A.flags & OM_RENDER_ADAPTIVE) != 0;
     const bool align = (A.flags & OM_RENDER_PHASE_ALIGN) != 0;
-    constexpr bool BOUNDED = OM_BOUNDED_MARCH_ALL || MA == 1 || MA == 3;  // scenes built around marched objects (C3); C2's kernel keeps march()
     Counters cn = {0, 0, 0, 0, 0, 0, 0};
-    unsigned long long credited = 0, traced = 0;
-    uint32_t warp_iters = 0, lane_iters = 0;  // COUNT: lane occupancy of the path loop
+    PathTotals T = {0ull, 0ull, 0u, 0u};
     const uint32_t lane = threadIdx.x & 31u;
     TravStack<SMEM, RENDER_THREADS> stack;  // shared memory behind the scene image when the scene is staged, else local memory
     stack.init(S.hot_units);
@@ -1294,89 +1407,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
         const bool touched = todo > 0u;
 
         // ---- per-lane path state machine; the loop itself is warp-uniform ----
-        Rng g;
-        rng_init(g, A.rk, 0u, 0u);
-        g.b0 = g.b1 = g.b2 = g.b3 = 0u;
-        Ray ray;
-        ray.o = v3(0.f, 0.f, 0.f); ray.d = v3(0.f, 0.f, 1.f);
-        V3 color = v3(1.f, 1.f, 1.f);
-        uint32_t seg = 0;
-        float first_t = kInf;
-        uint32_t first_lo = 0, first_hi = 0;
-        bool fresh = true;
-        bool marching = false;          // BOUNDED: the lane's ray is part-way through its march
-        float m_t = 0.f, pend_t = 0.f;  // ... how far, and the traced hit that stands if the march finds nothing
-        uint32_t m_left = 0xFFFFFFFFu, pend_ref = omd::REF_NONE;
-        while (__any_sync(FULL, todo > 0u)) {
-            const bool alive = todo > 0u;
-            if (COUNT) { warp_iters++; lane_iters += alive ? 1u : 0u; }
-            if (align) phase_bar_count(1);
-            if (alive && fresh) {
-                const uint32_t sample = A.sample_base + st.n;  // jitters[pixel.stats.n]
-                rng_init(g, A.rk, pxl, sample);
-                ray = primary_ray(A, pxl, sample, g);
-                color = v3(1.f, 1.f, 1.f);
-                seg = 0; first_t = kInf; first_lo = 0; first_hi = 0;
-                fresh = false;
-            }
-            Hit h;
-            bool resolved = alive;  // this lane's segment is resolved in this iteration (shade it)
-            if constexpr (BOUNDED) {
-                // Bounded marching: a lane whose ray enters the marched objects' bounds sphere-traces at most OM_MARCH_STEPS steps per
-                // iteration and carries on in the next one, while the other lanes of the warp shade, start samples and traverse.
-                // (One call of march() ran as long as the warp's longest march: 5.6 of 32 lanes per instruction on C3.)
-                const bool trav = alive && !marching;
-                if (COUNT && trav) cn.segments++;
-                const Best b = closest_traced_warp<SMEM, COUNT>(sv, S, ray, A.tmin, A.tmax, brute, trav, cn, stack);
-                h.t = pend_t; h.ref = pend_ref; h.point = v3(0.f, 0.f, 0.f); h.normal = v3(0.f, 0.f, 0.f);
-                if (trav) {
-                    h.t = b.t; h.ref = b.ref;
-                    if (S.n_marched != 0u) {  // (see closest_hit_warp)
-                        const RayInv q = ray_inv(ray);
-                        if (slab(S.march_lo[0], S.march_lo[1], S.march_lo[2], S.march_hi[0], S.march_hi[1], S.march_hi[2], q, A.tmin, fminf(A.tmax, b.t)) < kInf) {
-                            marching = true; m_left = 0xFFFFFFFFu; m_t = 0.f; pend_t = b.t; pend_ref = b.ref;
-                        }
-                    }
-                }
-                if (alive && marching) {
-                    Hit m;
-                    const bool over = march_some<SMEM, COUNT, MA == 1, MA == 3>(sv, S, ray, A.tmin, A.tmax, pend_t, m_t, m_left, OM_MARCH_STEPS, m, &cn);
-                    resolved = over;
-                    if (over) { marching = false; if (m.ref != omd::REF_NONE) h = m; else { h.t = pend_t; h.ref = pend_ref; } }
-                }
-            } else {
-                h = closest_hit_warp<SMEM, COUNT, MA>(sv, S, ray, A.tmin, A.tmax, brute, alive, cn, stack);
-            }
-            if (align) phase_bar();
-            if (resolved) {
-                bool finished;
-                V3 result = color;
-                if (h.ref != omd::REF_NONE) {  // handle_hit Some(hr), render_thread.rs:110-116
-                    finish_hit<SMEM, MA == 3>(sv, S, ray, A.tmin, h);
-                    const Material m = load_material(sv, S, h.ref);
-                    if (seg == 0u) { first_t = h.t; first_lo = m.bloom_lo; first_hi = m.bloom_hi; }
-                    color = color * scatter(m, ray, h.point, h.normal, g);
-                    seg++;
-                    finished = seg >= nseg;
-                    if (finished) result = -v3(0.f, 0.f, 0.f);  // out of depth: -black (:142)
-                } else {  // None: sky (:117-123)
-                    const float t = 0.5f * (ray.d.y + 1.0f);
-                    const V3 sky = (1.0f - t) * v3(1.f, 1.f, 1.f) + t * v3(0.5f, 0.7f, 1.0f);
-                    result = color * sky;
-                    finished = true;
-                }
-                if (finished) {
-                    bool done = stats_add(st, result, first_t, first_lo, first_hi);
-                    if (!adaptive) done = false;
-                    traced++;
-                    todo--;
-                    const uint32_t left = A.spp_budget - st.n;
-                    credited += (done ? (unsigned long long)left : 0ull) + 1ull;  // render_thread.rs:196-198
-                    if (done) todo = 0u;
-                    fresh = true;
-                }
-            }
-        }
+        PathLane L;
+        L.init(A.rk);
+        while (__any_sync(FULL, todo > 0u)) path_iteration<SMEM, COUNT, MA>(A, sv, S, brute, adaptive, align, nseg, pxl, st, todo, L, cn, T, stack);
         // ---- store Stats ----
         if (touched) {
             A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
@@ -1396,12 +1429,12 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
     }
     // ---- progress counters: warp-aggregate, one atomic per warp ----
     for (int o = 16; o > 0; o >>= 1) {
-        credited += __shfl_xor_sync(FULL, credited, o);
-        traced += __shfl_xor_sync(FULL, traced, o);
+        T.credited += __shfl_xor_sync(FULL, T.credited, o);
+        T.traced += __shfl_xor_sync(FULL, T.traced, o);
     }
     if ((threadIdx.x & 31) == 0) {
-        if (credited) atomicAdd(&A.counters[CTR_CREDITED], credited);
-        if (traced) atomicAdd(&A.counters[CTR_TRACED], traced);
+        if (T.credited) atomicAdd(&A.counters[CTR_CREDITED], T.credited);
+        if (T.traced) atomicAdd(&A.counters[CTR_TRACED], T.traced);
     }
     if (COUNT) {
         unsigned long long v[7] = {cn.segments, cn.node_visits, cn.prim_tests, cn.sdf_evals, cn.march_steps, cn.normal_evals, cn.march_entered};
@@ -1409,9 +1442,120 @@ __global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render(c
             for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
             if ((threadIdx.x & 31) == 0 && v[i]) atomicAdd(&A.counters[CTR_SEGMENTS + i], v[i]);
         }
-        unsigned long long li = lane_iters;
+        unsigned long long li = T.lane_iters;
         for (int o = 16; o > 0; o >>= 1) li += __shfl_xor_sync(0xffffffffu, li, o);
-        if ((threadIdx.x & 31) == 0) { atomicAdd(&A.counters[CTR_WARP_ITERS], (unsigned long long)warp_iters); atomicAdd(&A.counters[CTR_LANE_ITERS], li); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&A.counters[CTR_WARP_ITERS], (unsigned long long)T.warp_iters); atomicAdd(&A.counters[CTR_LANE_ITERS], li); }
+    }
+}
+
+// ============================================================================================
+// k_render_lanes: k_render with a work slot per LANE instead of a tile per warp, for adaptive passes.  There a warp that owns
+// a tile is held by the pixel that retires last while the others' lanes idle (lane occupancy of the adaptive passes 0.4-0.66;
+// a single 256-spp adaptive launch reaches 800 Msamples/s where fixed spp reaches 1850).  Here a lane whose pixel is done
+// stores it and takes the next unstarted slot at once.  The warps of a group (the 8 that share an SM sub-partition and, with
+// phase alignment, its barriers) draw from a shared run of OM_LANE_RUN consecutive slots - a 16 x 16-pixel block in tile
+// order (work_to_pixel) or a stretch of the live list, which is in tile order too: neighbouring pixels, similar work.
+// A pixel's samples still run in order in one lane: bit-identical.  (For FIXED spp the same scheme loses to tiles: occupancy
+// is 0.9 there already and mixing the pixels of a warp costs more than it gains, profiles/r2_experiments.md section 6.)
+// ============================================================================================
+#ifndef OM_LANE_RUN
+#define OM_LANE_RUN 256
+#endif
+template <bool SMEM, int MA>
+__global__ void __launch_bounds__(RENDER_THREADS, OM_RENDER_MIN_CTAS) k_render_lanes(const __grid_constant__ RenderArgs A) {
+    if (A.spread_max != 0u && A.live_count != nullptr && *A.live_count <= A.spread_max) return;  // k_render_spread's pass
+    if (SMEM) stage_scene_smem(A.hot_g, A.scene.hot_units);
+    SceneView<SMEM> sv;
+    sv.hot_g = A.hot_g;
+    sv.cold_g = A.cold_g;
+    const SceneHeader& S = A.scene;
+    const bool brute = (A.flags & OM_RENDER_BRUTE_FORCE) != 0;
+    const bool adaptive = (A.flags & OM_RENDER_ADAPTIVE) != 0;
+    const bool align = (A.flags & OM_RENDER_PHASE_ALIGN) != 0;
+    Counters cn = {0, 0, 0, 0, 0, 0, 0};
+    PathTotals T = {0ull, 0ull, 0u, 0u};
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+    TravStack<SMEM, RENDER_THREADS> stack;
+    stack.init(S.hot_units);
+    const uint32_t nseg = A.max_depth > 1u ? A.max_depth : 1u;
+    const uint32_t n_slots = A.live_list ? min(A.n_work, *A.live_count) : A.n_work;
+    __shared__ unsigned grp_lock[PB_GROUPS], grp_next[PB_GROUPS], grp_end[PB_GROUPS];
+    if (threadIdx.x < (unsigned)PB_GROUPS) { grp_lock[threadIdx.x] = 0u; grp_next[threadIdx.x] = 0u; grp_end[threadIdx.x] = 0u; }
+    __syncthreads();
+
+    uint32_t pxl = 0xFFFFFFFFu, todo = 0;
+    bool touched = false;    // the lane holds a pixel whose Stats changed
+    bool exhausted = false;  // (warp-uniform) no slots left
+    Stats st;
+    st.sum = v3(0.f, 0.f, 0.f); st.n = 0; st.avg_depth = 0.f; st.bad_avgs = 0; st.bloom_lo = 0; st.bloom_hi = 0; st.color = 0;
+    PathLane L;
+    L.init(A.rk);
+    for (;;) {
+        // ---- lanes without work: store the finished pixel, take the next slot ----
+        const unsigned m_need = __ballot_sync(FULL, todo == 0u);
+        if (m_need != 0u) {
+            if (todo == 0u && touched) {
+                A.acc[pxl] = make_float4(st.sum.x, st.sum.y, st.sum.z, __uint_as_float(st.n));
+                A.aux[pxl] = make_uint4(__float_as_uint(st.avg_depth), st.bad_avgs, st.bloom_lo, st.bloom_hi);
+                touched = false;
+            }
+            if (!exhausted) {
+                const uint32_t n_need = (uint32_t)__popc(m_need);
+                uint32_t b1 = 0, m1 = 0, b2 = 0;
+                if (lane == 0u) {  // n_need slots: what is left of the group's run, then the head of a new run
+                    const uint32_t gi = (threadIdx.x >> 5) % (unsigned)PB_GROUPS;
+                    while (atomicCAS(&grp_lock[gi], 0u, 1u) != 0u) {}
+                    __threadfence_block();
+                    const uint32_t have = grp_end[gi] - grp_next[gi];
+                    m1 = min(n_need, have);
+                    b1 = grp_next[gi];
+                    grp_next[gi] = b1 + m1;
+                    if (m1 < n_need) {
+                        b2 = (uint32_t)atomicAdd(&A.counters[CTR_TICKET], (unsigned long long)OM_LANE_RUN);  // (this kernel's unit of CTR_TICKET: one slot)
+                        grp_next[gi] = b2 + (n_need - m1);
+                        grp_end[gi] = b2 + (uint32_t)OM_LANE_RUN;
+                    }
+                    __threadfence_block();
+                    atomicExch(&grp_lock[gi], 0u);
+                }
+                b1 = __shfl_sync(FULL, b1, 0); m1 = __shfl_sync(FULL, m1, 0); b2 = __shfl_sync(FULL, b2, 0);
+                exhausted = (m1 > 0u ? b1 : b2) >= n_slots;
+                if (todo == 0u) {
+                    const uint32_t r = (uint32_t)__popc(m_need & lt_mask);
+                    const uint32_t k = r < m1 ? b1 + r : b2 + (r - m1);
+                    pxl = k < n_slots ? work_to_pixel(A, k) : 0xFFFFFFFFu;
+                    if (pxl != 0xFFFFFFFFu) {
+                        const float4 a = A.acc[pxl];
+                        const uint4 x = A.aux[pxl];
+                        st.sum = v3(a.x, a.y, a.z); st.n = __float_as_uint(a.w);
+                        st.avg_depth = __uint_as_float(x.x); st.bad_avgs = x.y; st.bloom_lo = x.z; st.bloom_hi = x.w;
+                        st.color = stats_color_of(st.sum, st.n);
+                        todo = A.spp_budget > st.n ? min(A.spp_budget - st.n, A.spp_pass) : 0u;
+                        if (A.n_target) { const uint32_t tg = min(A.spp_budget, A.n_target); todo = tg > st.n ? tg - st.n : 0u; }
+                        if (adaptive && st.bad_avgs >= 5u) todo = 0u;
+                        touched = todo > 0u;
+                        L.fresh = true;
+                    }
+                }
+            }
+        }
+        if (!__any_sync(FULL, todo > 0u)) {
+            if (exhausted) break;
+            continue;
+        }
+        path_iteration<SMEM, false, MA>(A, sv, S, brute, adaptive, align, nseg, pxl, st, todo, L, cn, T, stack);
+    }
+    // out of slots: keep answering the group's barriers until all of its warps are out
+    if (align) {
+        while (phase_bar_count(0) > 0) phase_bar();
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        T.credited += __shfl_xor_sync(FULL, T.credited, o);
+        T.traced += __shfl_xor_sync(FULL, T.traced, o);
+    }
+    if (lane == 0u) {
+        if (T.credited) atomicAdd(&A.counters[CTR_CREDITED], T.credited);
+        if (T.traced) atomicAdd(&A.counters[CTR_TRACED], T.traced);
     }
 }
 

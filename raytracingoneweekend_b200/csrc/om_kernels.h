@@ -10,6 +10,7 @@
     int render_occupancy(bool smem, bool count, size_t smem_bytes);                                                                \
     cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int grid, size_t smem_bytes, cudaStream_t st);      \
     cudaError_t launch_render_spread(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st);           \
+    cudaError_t launch_render_lanes(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st);            \
     /* CTA-resident wavefront (om_pool.cuh): shared-memory bytes behind the scene image, and the launch */                        \
     size_t pool_extra_smem(uint32_t stack_need);                                                                                   \
     int pool_occupancy(bool count, size_t smem_bytes);                                                                             \

@@ -47,6 +47,18 @@ cudaError_t launch_render(const omk::RenderArgs& a, bool smem, bool count, int g
     return cudaGetLastError();
 }
 
+// k_render_lanes<SMEM, MA> (adaptive passes: a work slot per lane; same block size and shared-memory layout as k_render)
+cudaError_t launch_render_lanes(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st) {
+    const int ma = scene_march_variant(a);
+    auto go = [&](auto kern) {
+        if (smem) prep(kern, smem_bytes);
+        kern<<<grid, RENDER_THREADS, smem ? smem_bytes : 0, st>>>(a);
+    };
+    if (smem) { if (ma == 1) go(k_render_lanes<true, 1>); else if (ma == 3) go(k_render_lanes<true, 3>); else go(k_render_lanes<true, 0>); }
+    else { if (ma == 1) go(k_render_lanes<false, 1>); else if (ma == 3) go(k_render_lanes<false, 3>); else go(k_render_lanes<false, 0>); }
+    return cudaGetLastError();
+}
+
 // k_render_spread<SMEM, MA> (adaptive passes with few live pixels; same block size and shared-memory layout as k_render)
 cudaError_t launch_render_spread(const omk::RenderArgs& a, bool smem, int grid, size_t smem_bytes, cudaStream_t st) {
     const int ma = scene_march_variant(a);
